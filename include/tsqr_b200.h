@@ -1,0 +1,80 @@
+/* tsqr_b200 -- thin C ABI over the B200-native tall-skinny QR library.
+ *
+ * The reference (enp1s0/tsqr-gpu) has no C ABI or FFI: its boundary is the C++ template
+ * API in include/tsqr/{tsqr,blockqr,tcqr}.hpp (reference src/tsqr.hpp:108-140,
+ * src/blockqr.hpp:142-175, src/tcqr.hpp:22-37). Each entry point below names the reference
+ * interface it stands in for. All matrices are column-major DEVICE memory (or pinned host
+ * memory mapped into the device), leading dimensions are in elements. `mode` is the
+ * numeric value of mtk::qr::compute_mode (reference src/tsqr.hpp:9-20):
+ *   0 fp16_notc  1 fp16_tc_nocor  2 fp32_notc  3 fp32_tc_cor  4 fp32_tc_nocor
+ *   5 mixed_tc_cor_emu  6 tf32_tc_cor  7 tf32_tc_cor_emu  8 tf32_tc_nocor  9 tf32_tc_nocor_emu
+ * Modes 0 and 1 take/return IEEE half elements, all others float.
+ *
+ * Return codes: 0 success, 1 invalid matrix size (reference error_invalid_matrix_size),
+ * negative = failure inside the library (see tsqr_b200_last_error()). Calls are ordered on
+ * `stream` (a cudaStream_t passed as void*; NULL = default stream) and do not block the host.
+ */
+#ifndef TSQR_B200_H
+#define TSQR_B200_H
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TSQR_B200_OK 0
+#define TSQR_B200_INVALID_SIZE 1
+#define TSQR_B200_ERR_ARGUMENT (-1)
+#define TSQR_B200_ERR_RUNTIME (-2)
+#define TSQR_B200_MAX_TSQR_N 64
+
+int tsqr_b200_version(void);
+const char* tsqr_b200_last_error(void);
+/* bytes per matrix element for `mode` (2 or 4); 0 if mode is invalid */
+size_t tsqr_b200_io_bytes(int mode);
+
+/* workspace size in bytes -- replaces mtk::qr::get_working_{q,r,l}_size
+ * (reference src/blockqr.cu:34-42) and mtk::qr::buffer::allocate (src/blockqr.hpp:76-95). */
+size_t tsqr_b200_qr_workspace_bytes(size_t m, size_t n, int reorthogonalize);
+/* replaces mtk::tsqr::get_working_{q,r}_size (reference src/tsqr.cu:47-60) */
+size_t tsqr_b200_tsqr_workspace_bytes(size_t m, size_t n);
+
+/* QR of A (m x n, any n <= m): Q (m x n), R (n x n upper block-triangular part written).
+ * A is overwritten when n > 64. Replaces mtk::qr::qr<mode, Reorthogonalize>
+ * (reference src/blockqr.hpp:142-175, src/blockqr.cu:394-433). */
+int tsqr_b200_qr(int mode, int reorthogonalize,
+                 void* q, size_t ldq, void* r, size_t ldr, void* a, size_t lda,
+                 size_t m, size_t n, void* workspace, size_t workspace_bytes, void* stream);
+
+/* TSQR of A (m x n, n <= 64), A is not modified. Replaces mtk::tsqr::tsqr16<mode>
+ * (reference src/tsqr.hpp:108-140, src/tsqr.cu:1281-1310). */
+int tsqr_b200_tsqr(int mode, void* q, size_t ldq, void* r, size_t ldr, const void* a, size_t lda,
+                   size_t m, size_t n, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Row-sharded (multi-GPU) TSQR in three steps; the reference is single-GPU only, these
+ * split tsqr16 (reference src/tsqr.cu:1064-1279) at its R-tree root:
+ *   1. reduce : local slab A_p (m_p x n) -> R_p (n x n float, ld n, upper triangular)
+ *   2. (caller) gather all R_p into an (P*n) x n float matrix, run tsqr_b200_tsqr on it
+ *      (mode 2) to get the final R and the (P*n) x n root factor; rows [p*n, p*n+n) of
+ *      the root factor are B_p
+ *   3. build  : Q_p = Qlocal_p * B_p (B_p n x n float, ld ldb; NULL = identity)
+ * The same workspace must be passed to reduce and build, untouched in between. */
+int tsqr_b200_tsqr_reduce(int mode, const void* a, size_t lda, size_t m, size_t n,
+                          float* r_local, void* workspace, size_t workspace_bytes, void* stream);
+int tsqr_b200_tsqr_build(int mode, void* q, size_t ldq, const void* a, size_t lda, size_t m, size_t n,
+                         const float* b, size_t ldb, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Batched QR of small row blocks (<= 32 rows x <= 16 columns each). Replaces
+ * mtk::tcqr::qr32x16_batched / qr32x16 (reference src/tcqr.hpp:22-37,
+ * src/tcqr32x16.cu:1584-1634). q/a element type follows `mode`; r is float unless the
+ * mode is a half mode. a_start_position has batch_size+1 entries (device memory). */
+int tsqr_b200_qr32x16_batched(int mode, void* q, size_t ldq, void* r, size_t ldr, const void* a, size_t lda,
+                              unsigned m, unsigned n, size_t batch_size, const unsigned* a_start_position,
+                              void* stream);
+
+/* how many kernels this library has launched in this process (bench bookkeeping) */
+unsigned long long tsqr_b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

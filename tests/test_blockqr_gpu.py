@@ -1,0 +1,53 @@
+"""GPU parity tests of BlockQR (n > 64) through the C ABI against LAPACK and the C restatement
+of the reference's block_qr_core / block_qr_reorthogonalization_core."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("m,n", [(4096, 128), (5000, 200), (2048, 65), (1024, 512)])
+@pytest.mark.parametrize("reorth", [False, True])
+def test_blockqr_uniform(cuda, oracle, m, n, reorth):
+    from helpers import run_qr
+    a = oracle.uniform_matrix(m, n, seed=n)
+    q, r, a_in = run_qr(a, "fp32_notc", reorth)
+    assert np.abs(np.tril(r, -1)).max() == 0.0
+    orth, res = oracle.orthogonality(q), oracle.residual(q, r, a_in)
+    st, qo, ro = oracle.ref_blockqr(a, reorth)
+    assert st == 0
+    # no worse than 2x the reference algorithm on the same input (small floor for fp32 noise)
+    assert orth <= max(2 * oracle.orthogonality(qo), 2e-6), (orth, oracle.orthogonality(qo))
+    assert res <= max(2 * oracle.residual(qo, ro, a), 2e-6), (res, oracle.residual(qo, ro, a))
+    _, rl = oracle.lapack_qr(a_in, np.float64)
+    assert oracle.r_rel_diff(r, rl) < 2e-5
+
+
+def test_blockqr_conditioned_reorth(cuda, oracle):
+    from helpers import run_qr
+    a = oracle.latms_matrix(8192, 160, 1e4, seed=5)
+    q0, r0, a_in = run_qr(a, "fp32_notc", False)
+    q1, r1, _ = run_qr(a, "fp32_notc", True)
+    _, qo0, ro0 = oracle.ref_blockqr(a, False)
+    _, qo1, ro1 = oracle.ref_blockqr(a, True)
+    assert oracle.orthogonality(q0) <= max(2 * oracle.orthogonality(qo0), 2e-6)
+    assert oracle.orthogonality(q1) <= max(2 * oracle.orthogonality(qo1), 2e-6)
+    assert oracle.orthogonality(q1) < 5e-6  # re-orthogonalisation restores O(eps)
+    assert oracle.residual(q1, r1, a_in) < 5e-6 and oracle.residual(q0, r0, a_in) < 5e-6
+
+
+def test_blockqr_half_io(cuda, oracle):
+    from helpers import run_qr
+    a = oracle.uniform_matrix(4096, 128, seed=8)
+    q, r, a_in = run_qr(a, "fp16_tc_nocor", True)
+    assert oracle.orthogonality(q) < 5e-3 and oracle.residual(q, r, a_in) < 5e-3
+
+
+def test_blockqr_overwrites_a_only_when_wide(cuda, oracle):
+    import tsqr_gpu_b200 as tq
+    a = tq.to_colmajor(torch.from_numpy(oracle.uniform_matrix(2000, 64, seed=1)).cuda())
+    a0 = a.clone()
+    tq.qr(a, "fp32_notc")
+    torch.cuda.synchronize()
+    assert torch.equal(a, a0)

@@ -1,0 +1,209 @@
+"""Python mirror of mtk::qr::qr / mtk::tsqr::tsqr16 / mtk::qr::buffer (reference
+src/blockqr.hpp:59-175, src/tsqr.hpp:49-140) on top of the C ABI.
+
+Matrices are torch CUDA tensors in column-major layout: shape (m, n), stride (1, ld).
+`to_colmajor` / `colmajor_empty` make such tensors. Everything runs on the current torch
+CUDA stream and never synchronises the host.
+"""
+import torch
+
+from ._lib import lib
+
+# numeric values of mtk::qr::compute_mode (reference src/tsqr.hpp:9-20)
+MODES = {
+    "fp16_notc": 0, "fp16_tc_nocor": 1, "fp32_notc": 2, "fp32_tc_cor": 3, "fp32_tc_nocor": 4,
+    "mixed_tc_cor_emu": 5, "tf32_tc_cor": 6, "tf32_tc_cor_emu": 7, "tf32_tc_nocor": 8, "tf32_tc_nocor_emu": 9,
+}
+MODE_NAMES = {v: k for k, v in MODES.items()}
+MAX_TSQR_N = 64
+
+
+class InvalidMatrixSize(ValueError):
+    """mtk::qr::error_invalid_matrix_size (state 1, reference src/blockqr.hpp:27-29)."""
+
+
+def _mode(mode):
+    if isinstance(mode, str):
+        return MODES[mode]
+    mode = int(mode)
+    if mode not in MODE_NAMES:
+        raise ValueError(f"unknown compute mode {mode}")
+    return mode
+
+
+def io_dtype(mode):
+    return torch.float16 if lib.tsqr_b200_io_bytes(_mode(mode)) == 2 else torch.float32
+
+
+def colmajor_empty(m, n, dtype, device="cuda", ld=None):
+    ld = m if ld is None else ld
+    return torch.empty((n, ld), dtype=dtype, device=device).t()[:m]
+
+
+def to_colmajor(x, ld=None):
+    """copy of a 2-D tensor in column-major storage (stride (1, ld))"""
+    m, n = x.shape
+    out = colmajor_empty(m, n, x.dtype, x.device, ld)
+    out.copy_(x)
+    return out
+
+
+def _check_colmajor(x, name):
+    if x.dim() != 2 or not x.is_cuda:
+        raise ValueError(f"{name}: expected a 2-D CUDA tensor")
+    if x.shape[0] > 1 and x.stride(0) != 1:
+        raise ValueError(f"{name}: expected column-major storage (stride(0) == 1), got strides {x.stride()}")
+    ld = x.stride(1) if x.shape[1] > 1 else max(x.shape[0], 1)
+    if ld < x.shape[0]:
+        raise ValueError(f"{name}: leading dimension {ld} < rows {x.shape[0]}")
+    return ld
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _raise(code):
+    if code == 0:
+        return
+    if code == 1:
+        raise InvalidMatrixSize("invalid matrix size (need 0 < n <= m)")
+    raise RuntimeError(f"tsqr_b200 error {code}: {lib.tsqr_b200_last_error().decode()}")
+
+
+class Buffer:
+    """Work buffer, the analogue of mtk::qr::buffer<mode, Reorthogonalize>::allocate(m, n).
+    One buffer per in-flight call. allocate twice -> RuntimeError like the reference."""
+
+    def __init__(self):
+        self.ws = None
+        self.total_memory_size = 0
+
+    def allocate(self, m, n, reorthogonalize=True, device="cuda"):
+        if self.ws is not None:
+            raise RuntimeError("The buffer has been already allocated")
+        nbytes = lib.tsqr_b200_qr_workspace_bytes(m, n, 1 if reorthogonalize else 0)
+        self.ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        self.total_memory_size = nbytes
+        return self
+
+    def destroy(self):
+        self.ws = None
+        self.total_memory_size = 0
+
+    def get_device_memory_size(self):
+        return self.total_memory_size
+
+
+def _workspace(buffer, m, n, reorth, device):
+    if buffer is None:
+        buffer = Buffer().allocate(m, n, reorth, device)
+    elif buffer.ws is None:
+        buffer.allocate(m, n, reorth, device)
+    return buffer
+
+
+def qr(a, mode="fp32_notc", reorthogonalize=False, buffer=None, q=None, r=None):
+    """mtk::qr::qr<mode, reorthogonalize>: returns (q, r). `a` is overwritten when n > 64."""
+    md = _mode(mode)
+    m, n = a.shape
+    if n > m or m == 0 or n == 0:
+        raise InvalidMatrixSize("invalid matrix size (need 0 < n <= m)")
+    if a.dtype != io_dtype(md):
+        raise TypeError(f"mode {MODE_NAMES[md]} takes {io_dtype(md)} matrices, got {a.dtype}")
+    lda = _check_colmajor(a, "a")
+    if q is None:
+        q = colmajor_empty(m, n, a.dtype, a.device)
+    if r is None:
+        r = torch.zeros((n, n), dtype=a.dtype, device=a.device).t()
+    ldq = _check_colmajor(q, "q")
+    ldr = _check_colmajor(r, "r")
+    buffer = _workspace(buffer, m, n, reorthogonalize, a.device)
+    code = lib.tsqr_b200_qr(md, 1 if reorthogonalize else 0, q.data_ptr(), ldq, r.data_ptr(), ldr, a.data_ptr(), lda,
+                            m, n, buffer.ws.data_ptr(), buffer.ws.numel(), _stream())
+    _raise(code)
+    return q, r
+
+
+def tsqr(a, mode="fp32_notc", buffer=None, q=None, r=None):
+    """mtk::tsqr::tsqr16<mode> widened to n <= 64: returns (q, r); `a` is not modified."""
+    md = _mode(mode)
+    m, n = a.shape
+    if a.dtype != io_dtype(md):
+        raise TypeError(f"mode {MODE_NAMES[md]} takes {io_dtype(md)} matrices, got {a.dtype}")
+    lda = _check_colmajor(a, "a")
+    if q is None:
+        q = colmajor_empty(m, n, a.dtype, a.device)
+    if r is None:
+        r = torch.zeros((n, n), dtype=a.dtype, device=a.device).t()
+    ldq = _check_colmajor(q, "q")
+    ldr = _check_colmajor(r, "r")
+    if buffer is None:
+        nbytes = lib.tsqr_b200_tsqr_workspace_bytes(m, n)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=a.device)
+    else:
+        ws = _workspace(buffer, m, n, True, a.device).ws
+    code = lib.tsqr_b200_tsqr(md, q.data_ptr(), ldq, r.data_ptr(), ldr, a.data_ptr(), lda, m, n, ws.data_ptr(),
+                              ws.numel(), _stream())
+    _raise(code)
+    return q, r
+
+
+def tsqr_reduce(a, mode, ws):
+    """step 1 of the row-sharded TSQR: local slab -> local R (n x n float32, column-major)"""
+    md = _mode(mode)
+    m, n = a.shape
+    lda = _check_colmajor(a, "a")
+    r_local = torch.empty((n, n), dtype=torch.float32, device=a.device).t()
+    code = lib.tsqr_b200_tsqr_reduce(md, a.data_ptr(), lda, m, n, r_local.data_ptr(), ws.data_ptr(), ws.numel(),
+                                     _stream())
+    _raise(code)
+    return r_local
+
+
+def tsqr_build(a, mode, ws, b=None, q=None):
+    """step 3 of the row-sharded TSQR: Q_local * B (B n x n float32 column-major or None)"""
+    md = _mode(mode)
+    m, n = a.shape
+    lda = _check_colmajor(a, "a")
+    if q is None:
+        q = colmajor_empty(m, n, a.dtype, a.device)
+    ldq = _check_colmajor(q, "q")
+    bptr, ldb = None, 0
+    if b is not None:
+        if b.dtype != torch.float32:
+            raise TypeError("b must be float32")
+        ldb = _check_colmajor(b, "b")
+        bptr = b.data_ptr()
+    code = lib.tsqr_b200_tsqr_build(md, q.data_ptr(), ldq, a.data_ptr(), lda, m, n, bptr, ldb, ws.data_ptr(),
+                                    ws.numel(), _stream())
+    _raise(code)
+    return q
+
+
+def qr32x16_batched(a, starts, n, mode="fp32_notc"):
+    """mtk::tcqr::qr32x16_batched: `a` (m x n col-major), `starts` int32 tensor of batch+1 row offsets.
+    Returns (q (m x n), r ((n*batch) x n))."""
+    md = _mode(mode)
+    m = a.shape[0]
+    batch = starts.numel() - 1
+    lda = _check_colmajor(a, "a")
+    q = colmajor_empty(m, n, a.dtype, a.device)
+    r = colmajor_empty(n * batch, n, a.dtype, a.device)
+    code = lib.tsqr_b200_qr32x16_batched(md, q.data_ptr(), m, r.data_ptr(), n * batch, a.data_ptr(), lda, m, n, batch,
+                                         starts.data_ptr(), _stream())
+    _raise(code)
+    return q, r
+
+
+def qr_host(a_host, q_host, r_host, a_dev, q_dev, r_dev, mode, reorthogonalize, buffer):
+    """End-to-end call with HOST buffers (pinned, column-major as (n, m) row-major arrays):
+    H2D of A, factorisation, D2H of Q and R, all on the current stream. Used for bench e2e."""
+    a_dev.t().copy_(a_host, non_blocking=True)
+    qr(a_dev, mode, reorthogonalize, buffer, q_dev, r_dev)
+    q_host.copy_(q_dev.t(), non_blocking=True)
+    r_host.copy_(r_dev.t(), non_blocking=True)
+
+
+def launch_count():
+    return int(lib.tsqr_b200_launch_count())

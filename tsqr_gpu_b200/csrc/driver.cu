@@ -1,0 +1,154 @@
+#include "driver.h"
+#include "common.cuh"
+#include <algorithm>
+#include <mutex>
+
+namespace tsqr_b200 {
+
+int device_sm_count() {
+  static int cached[64];
+  static std::once_flag once;
+  std::call_once(once, [] { for (int& c : cached) c = 0; });
+  int dev = 0;
+  // size queries must also work on a host without a device (planning is pure host logic)
+  if (cudaGetDevice(&dev) != cudaSuccess) { (void)cudaGetLastError(); return 148; }
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (cached[dev] == 0) {
+    int sms = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) { (void)cudaGetLastError(); sms = 0; }
+    cached[dev] = sms > 0 ? sms : 148;
+  }
+  return cached[dev];
+}
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+Plan make_plan(long long m, int n, int max_chunks0) {
+  Plan plan;
+  plan.m = m;
+  plan.n = n;
+  plan.np = (n + kPanel - 1) / kPanel * kPanel;
+  const int H = pass_tile_rows(plan.np);
+  const int sms = max_chunks0 > 0 ? 1 : device_sm_count();
+  size_t off = 0;
+  long long rows = m;
+  int level = 0;
+  while (true) {
+    Level L;
+    L.rows = rows;
+    const long long ntiles = (rows + H - 1) / H;
+    long long want;
+    if (level == 0) {
+      want = max_chunks0 > 0 ? max_chunks0
+                             : (long long)sms * pass_simt_max_ctas_per_sm(plan.np, true);
+    } else {
+      // upper levels: short chains (4 tiles per CTA) keep the tree shallow in time
+      want = (ntiles + 3) / 4;
+    }
+    if (ntiles <= 4) want = 1;
+    long long tiles_pc = (ntiles + want - 1) / want;
+    if (tiles_pc < 1) tiles_pc = 1;
+    L.rows_per_chunk = tiles_pc * H;
+    L.tiles_per_chunk = (int)tiles_pc;
+    L.nchunks = (int)((rows + L.rows_per_chunk - 1) / L.rows_per_chunk);
+    L.ckpt_off = off;
+    off = align_up(off + (size_t)L.nchunks * L.tiles_per_chunk * ckpt_floats(plan.np), 64);
+    L.S_off = off;
+    off = align_up(off + (size_t)L.nchunks * n * n, 64);
+    L.Qup_off = off;
+    off = align_up(off + (size_t)L.nchunks * n * n, 64);
+    plan.levels.push_back(L);
+    if (L.nchunks == 1) break;
+    rows = (long long)L.nchunks * n;
+    ++level;
+  }
+  plan.total_floats = off;
+  return plan;
+}
+
+size_t tsqr_workspace_bytes(long long m, int n) {
+  return make_plan(m, n).total_floats * sizeof(float) + 256;
+}
+
+static PassParams level_params(const Plan& plan, size_t li, const void* a, long long lda, float* ws) {
+  const Level& L = plan.levels[li];
+  PassParams p{};
+  p.n = plan.n;
+  p.np = plan.np;
+  p.M = L.rows;
+  p.nchunks = L.nchunks;
+  p.rows_per_chunk = L.rows_per_chunk;
+  p.tiles_per_chunk = L.tiles_per_chunk;
+  p.ckpt = ws + L.ckpt_off;
+  if (li == 0) {
+    p.A = a;
+    p.lda = lda;
+  } else {
+    p.A = ws + plan.levels[li - 1].S_off;
+    p.lda = L.rows;
+  }
+  p.S = ws + L.S_off;
+  p.lds = (long long)L.nchunks * plan.n;
+  return p;
+}
+
+const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long lda, float* ws, cudaStream_t s) {
+  for (size_t li = 0; li < plan.levels.size(); ++li) {
+    PassParams p = level_params(plan, li, a, lda, ws);
+    launch_pass_simt(p, false, li == 0 ? mode_io(mode) : IoType::f32, IoType::f32, s);
+  }
+  return ws + plan.levels.back().S_off;
+}
+
+void tsqr_build(const Plan& plan, int mode, const void* a, long long lda, void* q, long long ldq,
+                const float* B, long long ldb, float* ws, cudaStream_t s) {
+  for (size_t li = plan.levels.size(); li-- > 0;) {
+    const Level& L = plan.levels[li];
+    PassParams p = level_params(plan, li, a, lda, ws);
+    if (li + 1 == plan.levels.size()) {
+      p.Bsrc = B;
+      p.ldb = ldb;
+    } else {
+      p.Bsrc = ws + L.Qup_off;
+      p.ldb = (long long)L.nchunks * plan.n;
+    }
+    if (li == 0) {
+      p.Q = q;
+      p.ldq = ldq;
+      launch_pass_simt(p, true, mode_io(mode), mode_io(mode), s);
+    } else {
+      p.Q = ws + plan.levels[li - 1].Qup_off;
+      p.ldq = L.rows;
+      launch_pass_simt(p, true, IoType::f32, IoType::f32, s);
+    }
+  }
+}
+
+namespace {
+template <typename T>
+__global__ void store_r_kernel(const float* __restrict__ r32, int n, T* r, long long ldr) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n * n; i += gridDim.x * blockDim.x) {
+    const int j = i % n, k = i / n;
+    io_store(r + j + (long long)k * ldr, j <= k ? r32[j + (long long)k * n] : 0.f);
+  }
+}
+}  // namespace
+
+void store_r(const float* r32, int n, void* r, long long ldr, IoType t, cudaStream_t s) {
+  const int blocks = std::min(32, (n * n + 255) / 256);
+  if (t == IoType::f32) store_r_kernel<float><<<blocks, 256, 0, s>>>(r32, n, (float*)r, ldr);
+  else store_r_kernel<__half><<<blocks, 256, 0, s>>>(r32, n, (__half*)r, ldr);
+  note_launch();
+  TSQR_CUDA_CHECK(cudaGetLastError());
+}
+
+void tsqr_full(int mode, void* q, long long ldq, void* r, long long ldr, const void* a, long long lda,
+               long long m, int n, float* ws, size_t ws_bytes, cudaStream_t s) {
+  Plan plan = make_plan(m, n);
+  if (plan.total_floats * sizeof(float) > ws_bytes) throw std::runtime_error("tsqr_b200: workspace too small");
+  const float* r32 = tsqr_reduce(plan, mode, a, lda, ws, s);
+  store_r(r32, n, r, ldr, mode_io(mode), s);
+  tsqr_build(plan, mode, a, lda, q, ldq, nullptr, 0, ws, s);
+}
+
+}  // namespace tsqr_b200

@@ -1,0 +1,63 @@
+// Host driver: level planning, workspace carving and the TSQR / BlockQR call sequences.
+// Everything here is stream-ordered; no host synchronisation happens inside a call
+// (the reference synchronises 2L+3 times per 16-column panel, src/tsqr.cu:1112-1260).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstddef>
+#include <vector>
+#include "ts_pass.h"
+
+namespace tsqr_b200 {
+
+// numeric enum shared by mtk::qr / mtk::tsqr / mtk::tcqr (reference src/tsqr.hpp:9-20)
+enum Mode : int {
+  fp16_notc = 0, fp16_tc_nocor = 1, fp32_notc = 2, fp32_tc_cor = 3, fp32_tc_nocor = 4,
+  mixed_tc_cor_emu = 5, tf32_tc_cor = 6, tf32_tc_cor_emu = 7, tf32_tc_nocor = 8, tf32_tc_nocor_emu = 9,
+  kNumModes = 10
+};
+inline bool mode_valid(int m) { return m >= 0 && m < kNumModes; }
+inline IoType mode_io(int m) { return (m == fp16_notc || m == fp16_tc_nocor) ? IoType::f16 : IoType::f32; }
+inline size_t io_bytes(IoType t) { return t == IoType::f16 ? 2 : 4; }
+
+struct Level {
+  long long rows;
+  int nchunks;
+  long long rows_per_chunk;
+  int tiles_per_chunk;
+  size_t ckpt_off;   // float offsets into the workspace
+  size_t S_off;      // stacked R written by this level's reduce: (nchunks*n) x n
+  size_t Qup_off;    // Q of the next level (same shape as S), the B source of this level
+};
+
+struct Plan {
+  long long m;
+  int n, np;
+  std::vector<Level> levels;
+  size_t total_floats;
+};
+
+int device_sm_count();
+// levels for an m x n TSQR (n <= kMaxN). max_chunks0 <= 0 picks 1 CTA wave per SM x occupancy.
+Plan make_plan(long long m, int n, int max_chunks0 = 0);
+size_t tsqr_workspace_bytes(long long m, int n);
+
+// A (m x n) -> R_local (n x n fp32, column-major ld n, upper triangular, inside the
+// workspace at the returned pointer) and the checkpoints needed by tsqr_build.
+const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long lda, float* ws, cudaStream_t s);
+// Q = Q_local * B, with B (n x n fp32, column-major ldb) or identity when B == nullptr.
+void tsqr_build(const Plan& plan, int mode, const void* a, long long lda, void* q, long long ldq,
+                const float* B, long long ldb, float* ws, cudaStream_t s);
+// copy the upper triangle of an n x n fp32 matrix into the user's R (io type), zero below.
+void store_r(const float* r32, int n, void* r, long long ldr, IoType t, cudaStream_t s);
+
+// Full single-GPU TSQR, n <= kMaxN.
+void tsqr_full(int mode, void* q, long long ldq, void* r, long long ldr, const void* a, long long lda,
+               long long m, int n, float* ws, size_t ws_bytes, cudaStream_t s);
+
+// BlockQR for any n <= m (panels of kMaxN columns); overwrites A when n > kMaxN
+// (reference src/blockqr.cu:45-178, :180-390).
+size_t qr_workspace_bytes(long long m, long long n, bool reorth);
+int qr_full(int mode, bool reorth, void* q, long long ldq, void* r, long long ldr, void* a, long long lda,
+            long long m, long long n, float* ws, size_t ws_bytes, cudaStream_t s);
+
+}  // namespace tsqr_b200
