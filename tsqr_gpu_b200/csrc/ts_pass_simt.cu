@@ -95,37 +95,58 @@ struct Smem {
   float* Wsm;   // 256
   float* Ssm;   // 768     (build) Y_prev^T V_p
   float* Xsm;   // 768     (build) S * T_p
+  float* rowb;  // 2*16    (first tile) broadcast of the pivot row of the panel
 };
 
 __host__ __device__ inline size_t smem_floats(int np, int H, bool build) {
-  size_t f = (size_t)np * np * 2 + (size_t)np * H + 2048 + 256 + 256;
+  size_t f = (size_t)np * np * 2 + (size_t)np * H + 2048 + 256 + 256 + 32;
   if (build) f += (size_t)np * np + 768 + 768;
   return f;
 }
 
 
 // One Householder column step of the panel sweep (J = column inside the panel, compile-time
-// so that every register-array index is static). Reflector = [e_jj ; v], v = a[:,J]/(alpha-beta).
-template <int J, int RPT>
+// so that every register-array index is static).
+//  FIRST == false ("TS" step): the pivot row lives in the running R (Rs), the reflector is
+//      [e_jj ; v] with v = a[:,J]/(alpha-beta) over all tile rows.
+//  FIRST == true (first tile of a chunk, plain Householder): the pivot row is tile row jj
+//      (thread jj, r = 0); rows <= jj are masked out of the sums and keep their R entries.
+template <int J, int RPT, bool FIRST>
 __device__ __forceinline__ void sweep_step(float (&a)[RPT][16], const Smem& sm, int np, int c0, int t, int lane,
                                            int warp, int& buf) {
   const int jj = c0 + J;
   float rrow[16];
+  if (!FIRST) {
 #pragma unroll
-  for (int k4 = 0; k4 < 4; ++k4) {
-    float4 v4 = *reinterpret_cast<const float4*>(sm.Rs + jj * np + c0 + k4 * 4);
-    rrow[k4 * 4 + 0] = v4.x; rrow[k4 * 4 + 1] = v4.y; rrow[k4 * 4 + 2] = v4.z; rrow[k4 * 4 + 3] = v4.w;
+    for (int k4 = 0; k4 < 4; ++k4) {
+      float4 v4 = *reinterpret_cast<const float4*>(sm.Rs + jj * np + c0 + k4 * 4);
+      rrow[k4 * 4 + 0] = v4.x; rrow[k4 * 4 + 1] = v4.y; rrow[k4 * 4 + 2] = v4.z; rrow[k4 * 4 + 3] = v4.w;
+    }
+  } else if (t == jj) {
+#pragma unroll
+    for (int x = 0; x < 16; ++x) sm.rowb[buf * 16 + x] = a[0][x];
   }
+  const bool masked0 = FIRST && (t <= jj);  // row r=0 of this thread is at or above the pivot
+  float aj[RPT];
+#pragma unroll
+  for (int r = 0; r < RPT; ++r) aj[r] = (r == 0 && masked0) ? 0.f : a[r][J];
   float pr[16];
 #pragma unroll
   for (int x = 0; x < 16; ++x) {
-    pr[x] = __fmul_rn(a[0][J], a[0][x]);
+    pr[x] = __fmul_rn(aj[0], a[0][x]);
 #pragma unroll
-    for (int r = 1; r < RPT; ++r) pr[x] = __fmaf_rn(a[r][J], a[r][x], pr[x]);
+    for (int r = 1; r < RPT; ++r) pr[x] = __fmaf_rn(aj[r], a[r][x], pr[x]);
   }
   float* part = sm.part + buf * 1024;
   reduce16_store(pr, part, lane, warp);
   __syncthreads();
+  if (FIRST) {
+#pragma unroll
+    for (int k4 = 0; k4 < 4; ++k4) {
+      float4 v4 = *reinterpret_cast<const float4*>(sm.rowb + buf * 16 + k4 * 4);
+      rrow[k4 * 4 + 0] = v4.x; rrow[k4 * 4 + 1] = v4.y; rrow[k4 * 4 + 2] = v4.z; rrow[k4 * 4 + 3] = v4.w;
+    }
+  }
   buf ^= 1;
   float g[16];
 #pragma unroll
@@ -145,42 +166,49 @@ __device__ __forceinline__ void sweep_step(float (&a)[RPT][16], const Smem& sm, 
     const float coef = __fmul_rn(tau, s);
     const float cv = __fmul_rn(coef, rden);
 #pragma unroll
-    for (int r = 0; r < RPT; ++r) a[r][k] = __fmaf_rn(-cv, a[r][J], a[r][k]);
-    if (t == k) sm.Rs[jj * np + c0 + k] = __fsub_rn(rrow[k], coef);
-  }
-  if (t == J) {
-    sm.Rs[jj * np + jj] = beta;
-    sm.Ts[jj * np + jj] = tau;
+    for (int r = 0; r < RPT; ++r) a[r][k] = __fmaf_rn(-cv, aj[r], a[r][k]);
+    if (FIRST) {
+      if (t == jj) a[0][k] = __fsub_rn(rrow[k], coef);
+    } else {
+      if (t == k) sm.Rs[jj * np + c0 + k] = __fsub_rn(rrow[k], coef);
+    }
   }
 #pragma unroll
-  for (int r = 0; r < RPT; ++r) a[r][J] = __fmul_rn(a[r][J], rden);
+  for (int r = 0; r < RPT; ++r) a[r][J] = (r == 0 && masked0) ? a[r][J] : __fmul_rn(a[r][J], rden);
+  if (t == jj) {  // jj < np <= 64 < 128 threads
+    if (FIRST) a[0][J] = beta;
+    else sm.Rs[jj * np + jj] = beta;
+    sm.Ts[jj * np + jj] = tau;
+  }
   // T_p column J: T[i][J] = -tau * sum_{l=i}^{J-1} T[i][l] * (v_l . v_J), computed by thread i < J
   if (t < J) {
     float acc = 0.f;
 #pragma unroll
     for (int l = 0; l < J; ++l) {
-      if (l >= t) acc = __fmaf_rn(sm.Ts[(c0 + t) * np + c0 + l], __fmul_rn(g[l], rden), acc);
+      float z = __fmul_rn(g[l], rden);
+      if (FIRST) z = __fadd_rn(z, rrow[l]);  // v_l at the pivot row times the unit entry of v_J
+      if (l >= t) acc = __fmaf_rn(sm.Ts[(c0 + t) * np + c0 + l], z, acc);
     }
     sm.Ts[(c0 + t) * np + jj] = __fmul_rn(-tau, acc);
   }
 }
 
-template <int J, int RPT>
+template <int J, int RPT, bool FIRST>
 struct Sweep {
   static __device__ __forceinline__ void run(float (&a)[RPT][16], const Smem& sm, int np, int c0, int t, int lane,
                                              int warp, int& buf) {
-    sweep_step<J, RPT>(a, sm, np, c0, t, lane, warp, buf);
-    Sweep<J + 1, RPT>::run(a, sm, np, c0, t, lane, warp, buf);
+    sweep_step<J, RPT, FIRST>(a, sm, np, c0, t, lane, warp, buf);
+    Sweep<J + 1, RPT, FIRST>::run(a, sm, np, c0, t, lane, warp, buf);
   }
 };
-template <int RPT>
-struct Sweep<16, RPT> {
+template <int RPT, bool FIRST>
+struct Sweep<16, RPT, FIRST> {
   static __device__ __forceinline__ void run(float (&)[RPT][16], const Smem&, int, int, int, int, int, int&) {}
 };
 
 // Factor [R ; A_tile]. On exit Rs holds the new R, Ys the reflector tails, Ts the 16x16
 // diagonal T blocks (and, when BUILD, the full upper-triangular T).
-template <int RPT, bool BUILD, typename TIn>
+template <int RPT, bool BUILD, bool FIRST, typename TIn>
 __device__ __forceinline__ void factor_tile(const PassParams& P, const Smem& sm, long long row0,
                                             long long row_end, int& buf) {
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -210,7 +238,8 @@ __device__ __forceinline__ void factor_tile(const PassParams& P, const Smem& sm,
 #pragma unroll
       for (int v = t; v < 256; v += kT) {
         const int c = v >> 4, k = v & 15;
-        sm.tot[v] = __fadd_rn(sum4(part + v * 4), sm.Rs[(q0 + c) * np + c0 + k]);
+        const float gsum = sum4(part + v * 4);
+        sm.tot[v] = FIRST ? gsum : __fadd_rn(gsum, sm.Rs[(q0 + c) * np + c0 + k]);
       }
       __syncthreads();
 #pragma unroll
@@ -219,7 +248,7 @@ __device__ __forceinline__ void factor_tile(const PassParams& P, const Smem& sm,
         float w = 0.f;
         for (int d = 0; d <= c; ++d) w = __fmaf_rn(sm.Ts[(q0 + d) * np + q0 + c], sm.tot[d * 16 + k], w);
         sm.Wsm[v] = w;
-        sm.Rs[(q0 + c) * np + c0 + k] = __fsub_rn(sm.Rs[(q0 + c) * np + c0 + k], w);
+        if (!FIRST) sm.Rs[(q0 + c) * np + c0 + k] = __fsub_rn(sm.Rs[(q0 + c) * np + c0 + k], w);
       }
       __syncthreads();
 #pragma unroll 4
@@ -240,7 +269,17 @@ __device__ __forceinline__ void factor_tile(const PassParams& P, const Smem& sm,
       // next use of tot/Wsm is behind the next gram16's __syncthreads
     }
     // ---- unblocked Householder sweep over the 16 panel columns ----
-    Sweep<0, RPT>::run(a, sm, np, c0, t, lane, warp, buf);
+    Sweep<0, RPT, FIRST>::run(a, sm, np, c0, t, lane, warp, buf);
+    if (FIRST && t < np) {
+      // rows 0..np-1 of the first tile hold R on and above the diagonal: move it to Rs and
+      // leave the unit-lower-trapezoidal reflector block in the registers
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        const int k = c0 + c;
+        if (t < k) { sm.Rs[t * np + k] = a[0][c]; a[0][c] = 0.f; }
+        else if (t == k) { sm.Rs[k * np + k] = a[0][c]; a[0][c] = 1.f; }
+      }
+    }
     // ---- publish the reflector tails ----
 #pragma unroll
     for (int r = 0; r < RPT; ++r)
@@ -290,7 +329,8 @@ __global__ void __launch_bounds__(kPassThreads) ts_pass_kernel(const PassParams 
   sm.part = sm.Ts + np * np;
   sm.tot = sm.part + 2048;
   sm.Wsm = sm.tot + 256;
-  sm.Bs = sm.Wsm + 256;
+  sm.rowb = sm.Wsm + 256;
+  sm.Bs = sm.rowb + 32;
   sm.Ssm = sm.Bs + np * np;
   sm.Xsm = sm.Ssm + 768;
 
@@ -315,7 +355,8 @@ __global__ void __launch_bounds__(kPassThreads) ts_pass_kernel(const PassParams 
           if (k < np) ck[(size_t)j * np - (size_t)j * (j - 1) / 2 + (k - j)] = sm.Rs[j * np + k];
         }
       }
-      factor_tile<RPT, false, TIn>(P, sm, cbeg + (long long)tile * H, cend, buf);
+      if (tile == 0) factor_tile<RPT, false, true, TIn>(P, sm, cbeg, cend, buf);
+      else factor_tile<RPT, false, false, TIn>(P, sm, cbeg + (long long)tile * H, cend, buf);
     }
     // stacked output block: rows [chunk*n, chunk*n+n)
     for (int i = t; i < n * n; i += kT) {
@@ -346,16 +387,34 @@ __global__ void __launch_bounds__(kPassThreads) ts_pass_kernel(const PassParams 
       }
       __syncthreads();
       const long long row0 = cbeg + (long long)tile * H;
-      factor_tile<RPT, true, TIn>(P, sm, row0, cend, buf);
+      if (tile == 0) factor_tile<RPT, true, true, TIn>(P, sm, row0, cend, buf);
+      else factor_tile<RPT, true, false, TIn>(P, sm, row0, cend, buf);
+      const int lane = t & 31, warp = t >> 5;
+      const float* Bin = sm.Bs;
+      if (tile == 0) {
+        // first tile: Q = [B;0] - V (T (V1^T B)); V1 = rows 0..np-1 of V. B' = V1^T B goes to Rs
+        // (R of this tile is not needed any more in the build pass).
+        for (int c = warp; c < np; c += 4) {
+          float acc0 = 0.f, acc1 = 0.f;
+          for (int i = c; i < np; ++i) {
+            const float v = sm.Ys[(size_t)c * H + i];
+            if (lane < np) acc0 = __fmaf_rn(v, sm.Bs[i * np + lane], acc0);
+            if (lane + 32 < np) acc1 = __fmaf_rn(v, sm.Bs[i * np + lane + 32], acc1);
+          }
+          if (lane < np) sm.Rs[c * np + lane] = acc0;
+          if (lane + 32 < np) sm.Rs[c * np + lane + 32] = acc1;
+        }
+        __syncthreads();
+        Bin = sm.Rs;
+      }
       // W2 = T * B, written over T row by row (a warp owns whole rows)
       {
-        const int lane = t & 31, warp = t >> 5;
         for (int c = warp; c < np; c += 4) {
           float acc0 = 0.f, acc1 = 0.f;
           for (int d = c; d < np; ++d) {
             const float tcd = sm.Ts[c * np + d];
-            if (lane < np) acc0 = __fmaf_rn(tcd, sm.Bs[d * np + lane], acc0);
-            if (lane + 32 < np) acc1 = __fmaf_rn(tcd, sm.Bs[d * np + lane + 32], acc1);
+            if (lane < np) acc0 = __fmaf_rn(tcd, Bin[d * np + lane], acc0);
+            if (lane + 32 < np) acc1 = __fmaf_rn(tcd, Bin[d * np + lane + 32], acc1);
           }
           __syncwarp();
           if (lane < np) sm.Ts[c * np + lane] = acc0;
@@ -369,7 +428,7 @@ __global__ void __launch_bounds__(kPassThreads) ts_pass_kernel(const PassParams 
 #pragma unroll
         for (int r = 0; r < RPT; ++r)
 #pragma unroll
-          for (int k = 0; k < 16; ++k) z[r][k] = 0.f;
+          for (int k = 0; k < 16; ++k) z[r][k] = (tile == 0 && r == 0 && t < np) ? sm.Bs[t * np + k0 + k] : 0.f;
         for (int c = 0; c < np; ++c) {
           float w[16];
 #pragma unroll
