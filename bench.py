@@ -1,0 +1,346 @@
+#!/usr/bin/env python
+"""Headline benchmark: TSQR GFLOP/s (+ HBM GB/s vs roofline) at M = 2^24 rows per GPU, N = 64,
+fp32_tc_cor -- BASELINE.json's metric -- on 1..8 B200s of one node.
+
+  python bench.py --gpus N --steps K --warmup W            # this library
+  python bench.py --impl reference --gpus N ...            # the reference's own GPU build
+  (N > 1: python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...)
+
+One "step" = one QR factorisation (Q and R) of the synthetic matrix through the public API
+(mtk::qr::qr<mode,false> semantics via the C ABI). Flops are the standard geqrf+orgqr count
+4 M N^2 - 4/3 N^3 for every implementation.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="new", choices=["new", "reference"])
+    ap.add_argument("--m-log2", type=int, default=24, help="rows per GPU = 2^this")
+    ap.add_argument("--n", type=int, default=64)
+    ap.add_argument("--mode", default="fp32_tc_cor")
+    ap.add_argument("--reorth", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def flops(m, n):
+    return 4.0 * m * n * n - 4.0 / 3.0 * n ** 3
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks / throttle reasons during the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [x.strip() for x in ln.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_input(m, n, dtype, seed):
+    """uniform(-1,1), generated on the device, column-major (m x n view of an (n, m) buffer)"""
+    g = torch.Generator(device="cuda")
+    g.manual_seed(seed)
+    buf = torch.empty((n, m), dtype=torch.float32, device="cuda")
+    buf.uniform_(-1.0, 1.0, generator=g)
+    return buf.to(dtype).t()
+
+
+def cpu_lapack_baseline(n, budget_s=12.0):
+    """multithreaded host LAPACK sgeqrf+sorgqr on a bounded sample of the same workload"""
+    from oracle import oracle as o
+    cores = len(os.sched_getaffinity(0))
+    m_s = 1 << 20
+    a = o.uniform_matrix(m_s, n, seed=1)
+    o.lapack_qr(a[: 1 << 16])  # warm the library
+    t0 = time.perf_counter(); o.lapack_qr(a); dt = time.perf_counter() - t0
+    reps, total = 1, dt
+    while total < budget_s and reps < 4:
+        t0 = time.perf_counter(); o.lapack_qr(a); d = time.perf_counter() - t0
+        total += d; reps += 1; dt = min(dt, d)
+    return {"value": flops(m_s, n) / dt / 1e9, "unit": "GFLOP/s", "cores": cores, "kind": "port",
+            "sample": f"host LAPACK sgeqrf+sorgqr (scipy OpenBLAS) on M=2^20 x N={n} fp32 slab of the workload, "
+                      f"best of {reps}, {dt * 1e3:.0f} ms"}
+
+
+def run_reference(args, rank, world):
+    """reference arm: the UNMODIFIED reference (mtk::qr::qr of enp1s0/tsqr-gpu built for sm_100 in
+    oracle/_ref) on the same metric/config. The reference is single-GPU and has no CPU path, so
+    rank 0 runs it on its GPU; if the build is missing, the host-LAPACK port is timed instead."""
+    if rank != 0:
+        return
+    import tsqr_gpu_b200 as tq
+    m, n = 1 << args.m_log2, args.n
+    md = tq.MODES[args.mode]
+    so = os.path.join(ROOT, "oracle", "_ref", "libref_tcqr.so")
+    base = {"impl": "reference", "metric": "tsqr_gflops", "unit": "GFLOP/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic"}
+    cfg = {"workload": f"TSQR M=2^{args.m_log2} N={n} {args.mode} (mtk::qr::qr<{args.mode},{str(args.reorth).lower()}>)",
+           "m": m, "n": n, "mode": args.mode}
+    if not os.path.exists(so) or not torch.cuda.is_available():
+        cb = cpu_lapack_baseline(n)
+        cb["sample"] = "reference GPU build unavailable; " + cb["sample"]
+        line = dict(base, value=cb["value"], ms_per_step=None, config=cfg, cpu_baseline=cb,
+                    e2e={"value": cb["value"], "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+        print(json.dumps(line)); return
+    lib = ctypes.CDLL(so)
+    vp, sz = ctypes.c_void_p, ctypes.c_size_t
+    lib.ref_gpu_qr.argtypes = [ctypes.c_int, ctypes.c_int, vp, sz, vp, sz, vp, sz, sz, sz, vp]
+    lib.ref_gpu_qr.restype = ctypes.c_int
+    dt = tq.io_dtype(args.mode)
+    a0 = make_input(m, n, dt, 0x5EED0003)
+    a = tq.colmajor_empty(m, n, dt)
+    q = tq.colmajor_empty(m, n, dt)
+    r = torch.zeros((n, n), dtype=dt, device="cuda").t()
+    stream = torch.cuda.current_stream().cuda_stream
+    times = []
+    for it in range(args.warmup + args.steps):
+        a.copy_(a0)  # the reference overwrites A for n > 16 (src/blockqr.cu:107-116): restore, untimed
+        r.zero_()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        st = lib.ref_gpu_qr(md, int(args.reorth), q.data_ptr(), m, r.data_ptr(), n, a.data_ptr(), m, m, n, stream)
+        e1.record(); torch.cuda.synchronize()
+        if st != 0:
+            print(json.dumps({"impl": "reference", "unavailable": f"reference qr returned {st}"})); return
+        if it >= args.warmup:
+            times.append(e0.elapsed_time(e1))
+    ms = float(np.mean(times))
+    val = flops(m, n) / (ms * 1e-3) / 1e9
+    balg = (3.0 * m * n + n * n) * (2 if dt == torch.float16 else 4)
+    line = dict(base, value=val, ms_per_step=ms, config=cfg,
+                hbm_gbs=balg / (ms * 1e-3) / 1e9,
+                cpu_baseline={"value": val, "unit": "GFLOP/s", "cores": 0, "kind": "reference",
+                              "sample": "reference's own GPU build (sm_100, oracle/_ref) on rank 0's B200, full workload; "
+                                        "the reference has no CPU path"},
+                e2e={"value": val, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+    print(json.dumps(line))
+
+
+def main():
+    args = parse()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        if torch.cuda.is_available():
+            torch.cuda.set_device(local_rank)
+        run_reference(args, rank, world)
+        return
+    import torch.distributed as dist
+    import tsqr_gpu_b200 as tq
+    from tsqr_gpu_b200._lib import lib
+    from tsqr_gpu_b200.dist import tsqr_sharded
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    P = world
+    m, n = 1 << args.m_log2, args.n      # rows PER GPU (weak scaling: total rows = P * m)
+    dt = tq.io_dtype(args.mode)
+    esz = 2 if dt == torch.float16 else 4
+    a = make_input(m, n, dt, 0x5EED0003 + rank)
+    a_pristine = a.clone() if n > 64 else None
+    q = tq.colmajor_empty(m, n, dt)
+    r = torch.zeros((n, n), dtype=dt, device="cuda").t()
+    buf = tq.Buffer().allocate(m, n, True)
+
+    def step():
+        if P > 1:
+            return tsqr_sharded(a, args.mode, buf.ws, q=q, world_size=P, rank=rank)
+        if a_pristine is not None:
+            a.copy_(a_pristine)
+        return tq.qr(a, args.mode, args.reorth, buf, q, r)
+
+    def barrier():
+        if P > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    lib.tsqr_b200_profile_enable(1)
+    launches0 = tq.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    launches = tq.launch_count() - launches0
+    lib.tsqr_b200_profile_enable(0)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = e0.elapsed_time(e1)
+    if P > 1:
+        tt = torch.tensor([ms_total], device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+    ms = ms_total / args.steps
+    # per-launch durations of the level passes (CUDA events on the launching stream)
+    cap = 64 * args.steps + 64
+    labels = (ctypes.c_int * cap)(); dur = (ctypes.c_float * cap)()
+    cnt = lib.tsqr_b200_profile_read(labels, dur, cap)
+    per = {}
+    for i in range(cnt):
+        per.setdefault(labels[i], []).append(dur[i])
+    t_reduce0 = float(np.mean(per.get(0, [float("nan")])))
+    t_build0 = float(np.mean(per.get(1, [float("nan")])))
+    t_upper = sum(float(np.sum(v)) for k, v in per.items() if k >= 2) / max(args.steps, 1)
+
+    # sanity of the result that was just timed: ||Q^T Q - I||_F / sqrt(n) (fp32 on device)
+    orth_probe = None
+    if P == 1:
+        qt = q.t().float() if q.t().is_contiguous() else q.t().contiguous().float()
+        g = torch.zeros((n, n), device="cuda", dtype=torch.float64)
+        step_rows = 1 << 20
+        for i in range(0, m, step_rows):
+            blk = qt[:, i:i + step_rows].double()
+            g += blk @ blk.t()
+        orth_probe = float((g - torch.eye(n, device="cuda", dtype=torch.float64)).norm() / n ** 0.5)
+        del g, qt
+
+    # ---- end-to-end through the public API with HOST buffers (H2D + D2H inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        a_host = torch.empty((n, m), dtype=dt, pin_memory=True)
+        q_host = torch.empty((n, m), dtype=dt, pin_memory=True)
+        r_host = torch.empty((n, n), dtype=torch.float32 if P > 1 else dt, pin_memory=True)
+        a_host.copy_(a.t() if a_pristine is None else a_pristine.t())
+        torch.cuda.synchronize()
+
+        def e2e_step():
+            a.t().copy_(a_host, non_blocking=True)
+            if P > 1:
+                _, rr = tsqr_sharded(a, args.mode, buf.ws, q=q, world_size=P, rank=rank)
+            else:
+                _, rr = tq.qr(a, args.mode, args.reorth, buf, q, r)
+            q_host.copy_(q.t(), non_blocking=True)
+            r_host.copy_(rr.t(), non_blocking=True)
+
+        e2e_steps = max(1, min(args.steps, 3))
+        e2e_step(); barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for _ in range(e2e_steps):
+            e2e_step()
+        f1.record()
+        barrier()
+        ems = f0.elapsed_time(f1)
+        if P > 1:
+            tt = torch.tensor([ems], device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ems = float(tt.item())
+        ems /= e2e_steps
+        e2e = {"value": flops(m * P, n) / (ems * 1e-3) / 1e9, "unit": "GFLOP/s", "ms_per_step": ems,
+               "steps": e2e_steps, "h2d_bytes_per_step": m * n * esz * P,
+               "d2h_bytes_per_step": (m * n * esz + n * n * 4) * P}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        balg_step = (3.0 * m * n + n * n) * esz            # per GPU
+        balg_build = 2.0 * m * n * esz                      # level-0 build pass: read A, write Q
+        achieved = balg_build / (t_build0 * 1e-3) / 1e9
+        line = {
+            "metric": "tsqr_gflops", "value": flops(m * P, n) / (ms * 1e-3) / 1e9, "unit": "GFLOP/s",
+            "n_gpus": P, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"TSQR M=2^{args.m_log2} per GPU x N={n} {args.mode} "
+                                   f"(mtk::qr::qr<{args.mode},{str(args.reorth).lower()}> via the C ABI), column-major, "
+                                   "uniform(-1,1) generated on device",
+                       "m_per_gpu": m, "m_total": m * P, "n": n, "mode": args.mode,
+                       "parallelism": f"row-sharded x{P}, one all-gather of the {n}x{n} R factors" if P > 1 else "single GPU",
+                       "l2": f"inputs ({m * n * esz / 2**30:.1f} GiB per GPU) are larger than the 126 MB L2; no flush needed"},
+            "hbm_gbs_per_gpu": balg_step / (ms * 1e-3) / 1e9,
+            "hbm_frac_step": balg_step / (ms * 1e-3) / 1e9 / peak,
+            "roofline": {"bound": "hbm", "kernel": "ts_pass_kernel<BUILD> level 0 (Q-build pass: read A + checkpoints, write Q)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "peak_source": peak_src, "algorithmic_bytes_per_launch": balg_build,
+                         "ms_per_launch": t_build0,
+                         "other_kernels_ms": {"reduce_level0": t_reduce0, "upper_levels_total": t_upper}},
+            "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e,
+            "orthogonality_probe": orth_probe,
+        }
+        if P == 1 and not args.no_cpu:
+            try:
+                line["cpu_baseline"] = cpu_lapack_baseline(n)
+            except Exception as ex:  # noqa: BLE001
+                line["cpu_baseline"] = {"value": None, "unit": "GFLOP/s", "cores": 0, "kind": "port", "sample": f"failed: {ex}"}
+        print(json.dumps(line))
+    if P > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -71,6 +71,13 @@ int tsqr_b200_qr32x16_batched(int mode, void* q, size_t ldq, void* r, size_t ldr
                               unsigned m, unsigned n, size_t batch_size, const unsigned* a_start_position,
                               void* stream);
 
+/* Optional per-launch timing of the TSQR level passes with CUDA events on the caller's stream
+ * (the analogue of the reference's MEASURE_QR_TIME / PROFILE_BREAKDOWN compile-time switches,
+ * reference src/tsqr.cu:21-26, src/blockqr.cu:6-7). label = level * 2 + (1 for the Q-build
+ * pass, 0 for the R-reduce pass). Read after synchronising the stream. */
+void tsqr_b200_profile_enable(int on);
+int tsqr_b200_profile_read(int* labels, float* ms, int capacity);
+
 /* how many kernels this library has launched in this process (bench bookkeeping) */
 unsigned long long tsqr_b200_launch_count(void);
 

@@ -66,6 +66,8 @@ int tsqr_b200_version(void) { return 100; }
 const char* tsqr_b200_last_error(void) { return g_err; }
 size_t tsqr_b200_io_bytes(int mode) { return mode_valid(mode) ? io_bytes(mode_io(mode)) : 0; }
 unsigned long long tsqr_b200_launch_count(void) { return g_launches.load(); }
+void tsqr_b200_profile_enable(int on) { profile_enable(on != 0); }
+int tsqr_b200_profile_read(int* labels, float* ms, int cap) { return profile_read(labels, ms, cap); }
 
 size_t tsqr_b200_qr_workspace_bytes(size_t m, size_t n, int reorth) {
   if (m == 0 || n == 0 || n > m) return 256;

@@ -21,6 +21,37 @@ int device_sm_count() {
   return cached[dev];
 }
 
+namespace {
+struct ProfRec { int label; cudaEvent_t beg, end; };
+bool g_prof_on = false;
+std::vector<ProfRec> g_prof;
+std::mutex g_prof_mu;
+struct ProfScope {
+  cudaStream_t s; int label; cudaEvent_t beg = nullptr, end = nullptr; bool on;
+  ProfScope(cudaStream_t st, int lb) : s(st), label(lb), on(g_prof_on) {
+    if (on) { cudaEventCreate(&beg); cudaEventCreate(&end); cudaEventRecord(beg, s); }
+  }
+  ~ProfScope() {
+    if (on) { cudaEventRecord(end, s); std::lock_guard<std::mutex> lk(g_prof_mu); g_prof.push_back({label, beg, end}); }
+  }
+};
+}  // namespace
+
+void profile_enable(bool on) { g_prof_on = on; }
+int profile_read(int* labels, float* ms, int cap) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  int n = 0;
+  for (auto& r : g_prof) {
+    float t = 0.f;
+    cudaEventSynchronize(r.end);
+    cudaEventElapsedTime(&t, r.beg, r.end);
+    if (n < cap) { labels[n] = r.label; ms[n] = t; ++n; }
+    cudaEventDestroy(r.beg); cudaEventDestroy(r.end);
+  }
+  g_prof.clear();
+  return n;
+}
+
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 Plan make_plan(long long m, int n, int max_chunks0) {
@@ -95,6 +126,7 @@ static PassParams level_params(const Plan& plan, size_t li, const void* a, long 
 const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long lda, float* ws, cudaStream_t s) {
   for (size_t li = 0; li < plan.levels.size(); ++li) {
     PassParams p = level_params(plan, li, a, lda, ws);
+    ProfScope prof(s, (int)li * 2);
     launch_pass_simt(p, false, li == 0 ? mode_io(mode) : IoType::f32, IoType::f32, s);
   }
   return ws + plan.levels.back().S_off;
@@ -105,6 +137,7 @@ void tsqr_build(const Plan& plan, int mode, const void* a, long long lda, void* 
   for (size_t li = plan.levels.size(); li-- > 0;) {
     const Level& L = plan.levels[li];
     PassParams p = level_params(plan, li, a, lda, ws);
+    ProfScope prof(s, (int)li * 2 + 1);
     if (li + 1 == plan.levels.size()) {
       p.Bsrc = B;
       p.ldb = ldb;

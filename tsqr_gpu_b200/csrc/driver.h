@@ -37,6 +37,11 @@ struct Plan {
 };
 
 int device_sm_count();
+
+// Optional per-launch timing of the level passes (CUDA events on the launching stream, read
+// back after the caller synchronised). label = level * 2 + (build ? 1 : 0).
+void profile_enable(bool on);
+int profile_read(int* labels, float* ms, int cap);  // returns #records copied, clears them
 // levels for an m x n TSQR (n <= kMaxN). max_chunks0 <= 0 picks 1 CTA wave per SM x occupancy.
 Plan make_plan(long long m, int n, int max_chunks0 = 0);
 size_t tsqr_workspace_bytes(long long m, int n);
