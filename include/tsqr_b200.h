@@ -78,6 +78,12 @@ int tsqr_b200_qr32x16_batched(int mode, void* q, size_t ldq, void* r, size_t ldr
 void tsqr_b200_profile_enable(int on);
 int tsqr_b200_profile_read(int* labels, float* ms, int capacity);
 
+/* Known-answer self test of the tcgen05/TMEM operand layouts used by the tensor-core kernels
+ * (no reference counterpart; the reference's analogue is src/wmma_extension/test/correctness).
+ * A, B: 128 x 64 col-major fp32 (ld 128), X: 64 x 64 (ld 64); D1..D4: 128 x 64 outputs. */
+int tsqr_b200_selftest_mma(int corrected, const float* A, const float* B, const float* X, float* D1,
+                           float* D2, float* D3, float* D4, void* stream);
+
 /* how many kernels this library has launched in this process (bench bookkeeping) */
 unsigned long long tsqr_b200_launch_count(void);
 

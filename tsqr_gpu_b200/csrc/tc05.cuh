@@ -1,0 +1,195 @@
+// tcgen05 / TMEM / mbarrier primitives for sm_100a, hand-written PTX (no CUTLASS on the path).
+//
+// Operand staging convention used by every tensor-core kernel of the library ("tile buffer"):
+// a rows x cols fp32 (tf32 container) matrix is kept in shared memory in the 128-byte-swizzled
+// UMMA canonical layout, cut into 1 KiB atoms of 32 rows x 8 columns:
+//
+//     atom(rb, cg)  at  (rb * (cols/8) + cg) * 1024 bytes          rb = row/32, cg = col/8
+//     inside an atom: (col%8)*128 + ((((row%32)/4) ^ (col%8)) * 16) + (row%4)*4
+//
+// The same bytes are a valid K-major operand with K = rows (MN = columns: used for the Gram
+// products V^T A, V^T V) and a valid MN-major operand with MN = rows (K = columns: used for the
+// updates A -= V W and Q = V X), so a reflector block is written once and used in both roles.
+// A warp that writes 32 consecutive rows of one column touches 32 distinct banks.
+//
+// hi/lo error correction: hi = tf32(x) rounded to nearest (cvt.rna), lo = x - hi (exact in
+// fp32, read by the tensor core as tf32). A corrected product is three MMAs into one fp32
+// TMEM accumulator: hi*hi + hi*lo + lo*hi. This is the split of reference
+// src/tsqr.cu:546-549 / src/tcqr32x16.cu:923-926 fused into the operand store.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace tsqr_b200 {
+namespace tc {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+// ---- tile buffer addressing (byte offset of element (row, col); cols = buffer width, multiple of 8)
+__device__ __forceinline__ uint32_t tile_off(int row, int col, int cols) {
+  const int rb = row >> 5, cg = col >> 3, c8 = col & 7, r32 = row & 31;
+  return (uint32_t)(((rb * (cols >> 3) + cg) << 10) + (c8 << 7) + ((((r32 >> 2) ^ c8)) << 4) + ((r32 & 3) << 2));
+}
+
+__device__ __forceinline__ float to_tf32_rna(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
+
+// store x into the hi (and, when COR, lo) tile buffers
+template <bool COR>
+__device__ __forceinline__ void tile_store(char* hi, char* lo, uint32_t off, float x) {
+  const float h = to_tf32_rna(x);
+  *reinterpret_cast<float*>(hi + off) = h;
+  if (COR) *reinterpret_cast<float*>(lo + off) = __fsub_rn(x, h);
+}
+
+// ---- descriptors
+// shared-memory matrix descriptor, SWIZZLE_128B, version 1 (Blackwell)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;  // descriptor version
+  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  return d;
+}
+
+// instruction descriptor for kind::tf32, fp32 accumulate
+__host__ __device__ constexpr uint32_t idesc_tf32(int M, int N, bool a_mn_major, bool b_mn_major, bool neg_a) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((neg_a ? 1u : 0u) << 13) | ((a_mn_major ? 1u : 0u) << 15) |
+         ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+__device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, bool accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"((uint32_t)accumulate)
+      : "memory");
+}
+
+// ---- mbarrier
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+// all previously issued tcgen05.mma of this thread arrive on `bar` when they complete
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+
+// ---- fences
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// ---- TMEM allocation (one full warp calls alloc / dealloc)
+template <int COLS>
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_result) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_result)), "n"(COLS)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS) : "memory");
+}
+
+// ---- TMEM <-> registers, shape 32x32b: thread (warp w, lane l) owns TMEM lane 32*(w%4)+l and
+// reads/writes consecutive 32-bit columns starting at the column of taddr.
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+      "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+      "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+      "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+      "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15]))
+      : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// TMEM address of (lane base of this warp, column)
+__device__ __forceinline__ uint32_t tmem_addr(uint32_t base, int warp, int col) {
+  return base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)col;
+}
+
+// ---- composite products on tile buffers (issued by ONE thread) ---------------------------
+// D[M=128 x N] (+)= sum over K = rows [0, krows) of  Acols^T * Bcols   (both K-major views)
+//   A buffer: a_cols wide, M index = column a_c0 + m (reads 128 columns: whatever lies behind
+//   the real ones only produces accumulator rows nobody reads); B buffer: b_cols wide, N
+//   index = column b_c0 + n. krows multiple of 8.
+template <bool COR>
+__device__ __forceinline__ void gram_issue(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_cols, int a_c0,
+                                           uint32_t b_hi, uint32_t b_lo, int b_cols, int b_c0, int N, int krows,
+                                           bool accumulate) {
+  const uint32_t id = idesc_tf32(128, N, false, false, false);
+  const uint32_t a_rb = (uint32_t)(a_cols >> 3) << 10, b_rb = (uint32_t)(b_cols >> 3) << 10;
+  const uint32_t a0 = (uint32_t)(a_c0 >> 3) << 10, b0 = (uint32_t)(b_c0 >> 3) << 10;
+  bool acc = accumulate;
+  for (int k = 0; k < krows; k += 8) {
+    const uint32_t ao = a0 + (uint32_t)(k >> 5) * a_rb + (uint32_t)(k & 31) * 4;
+    const uint32_t bo = b0 + (uint32_t)(k >> 5) * b_rb + (uint32_t)(k & 31) * 4;
+    mma_tf32(d_tmem, smem_desc(a_hi + ao, 16, 1024), smem_desc(b_hi + bo, 16, 1024), id, acc);
+    acc = true;
+    if (COR) {
+      mma_tf32(d_tmem, smem_desc(a_hi + ao, 16, 1024), smem_desc(b_lo + bo, 16, 1024), id, true);
+      mma_tf32(d_tmem, smem_desc(a_lo + ao, 16, 1024), smem_desc(b_hi + bo, 16, 1024), id, true);
+    }
+  }
+}
+
+// D[M=128 rows x N] (+)= (neg ? -1 : 1) * A[:, a_c0 : a_c0+kcols] * B     (A: MN-major view of a
+//   128-row tile buffer a_cols wide; B: K-major view of a buffer whose ROWS are the K index
+//   (kcols of them, starting at row b_k0) and whose columns are the N index from b_c0.
+template <bool COR>
+__device__ __forceinline__ void update_issue(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_cols, int a_c0,
+                                             uint32_t b_hi, uint32_t b_lo, int b_cols, int b_c0, int b_k0, int N,
+                                             int kcols, bool neg, bool accumulate) {
+  const uint32_t id = idesc_tf32(128, N, true, false, neg);
+  const uint32_t a_lbo = (uint32_t)(a_cols >> 3) << 10;  // next 32 rows
+  const uint32_t b_rb = (uint32_t)(b_cols >> 3) << 10;
+  bool acc = accumulate;
+  for (int k = 0; k < kcols; k += 8) {
+    const uint32_t ao = (uint32_t)((a_c0 + k) >> 3) << 10;
+    const int bk = b_k0 + k;
+    const uint32_t bo = ((uint32_t)(b_c0 >> 3) << 10) + (uint32_t)(bk >> 5) * b_rb + (uint32_t)(bk & 31) * 4;
+    mma_tf32(d_tmem, smem_desc(a_hi + ao, a_lbo, 1024), smem_desc(b_hi + bo, 16, 1024), id, acc);
+    acc = true;
+    if (COR) {
+      mma_tf32(d_tmem, smem_desc(a_hi + ao, a_lbo, 1024), smem_desc(b_lo + bo, 16, 1024), id, true);
+      mma_tf32(d_tmem, smem_desc(a_lo + ao, a_lbo, 1024), smem_desc(b_hi + bo, 16, 1024), id, true);
+    }
+  }
+}
+
+}  // namespace tc
+}  // namespace tsqr_b200
