@@ -57,9 +57,10 @@ int tsqr_b200_tsqr(int mode, void* q, size_t ldq, void* r, size_t ldr, const voi
  *      (mode 2) to get the final R and the (P*n) x n root factor; rows [p*n, p*n+n) of
  *      the root factor are B_p
  *   3. build  : Q_p = Qlocal_p * B_p (B_p n x n float, ld ldb; NULL = identity)
- * The same workspace must be passed to reduce and build, untouched in between. */
+ * The same workspace AND the same q (m_p x n, element type of `mode`) must be passed to reduce
+ * and build, untouched in between: the tensor-core modes keep the slab's reflectors in q. */
 int tsqr_b200_tsqr_reduce(int mode, const void* a, size_t lda, size_t m, size_t n,
-                          float* r_local, void* workspace, size_t workspace_bytes, void* stream);
+                          float* r_local, void* q, size_t ldq, void* workspace, size_t workspace_bytes, void* stream);
 int tsqr_b200_tsqr_build(int mode, void* q, size_t ldq, const void* a, size_t lda, size_t m, size_t n,
                          const float* b, size_t ldb, void* workspace, size_t workspace_bytes, void* stream);
 
@@ -81,7 +82,7 @@ int tsqr_b200_profile_read(int* labels, float* ms, int capacity);
 /* Known-answer self test of the tcgen05/TMEM operand layouts used by the tensor-core kernels
  * (no reference counterpart; the reference's analogue is src/wmma_extension/test/correctness).
  * A, B: 128 x 64 col-major fp32 (ld 128), X: 64 x 64 (ld 64); D1..D4: 128 x 64 outputs. */
-int tsqr_b200_selftest_mma(int corrected, const float* A, const float* B, const float* X, float* D1,
+int tsqr_b200_selftest_mma(int corrected, int variant, const float* A, const float* B, const float* X, float* D1,
                            float* D2, float* D3, float* D4, void* stream);
 
 /* how many kernels this library has launched in this process (bench bookkeeping) */

@@ -15,15 +15,16 @@ def _cm(x):  # column-major device copy, returned flat
     return torch.from_numpy(np.asfortranarray(x).ravel(order="F").copy()).cuda()
 
 
+@pytest.mark.parametrize("variant", [0, 1])
 @pytest.mark.parametrize("corrected", [0, 1])
-def test_mma_selftest(cuda, corrected):
+def test_mma_selftest(cuda, corrected, variant):
     rng = np.random.default_rng(7)
     A = rng.uniform(-1, 1, (128, 64)).astype(np.float32)
     B = rng.uniform(-1, 1, (128, 64)).astype(np.float32)
     X = rng.uniform(-1, 1, (64, 64)).astype(np.float32)
     dA, dB, dX = _cm(A), _cm(B), _cm(X)
     outs = [torch.zeros(128 * 64, dtype=torch.float32, device="cuda") for _ in range(4)]
-    rc = lib.tsqr_b200_selftest_mma(corrected, dA.data_ptr(), dB.data_ptr(), dX.data_ptr(),
+    rc = lib.tsqr_b200_selftest_mma(corrected, variant, dA.data_ptr(), dB.data_ptr(), dX.data_ptr(),
                                     *[o.data_ptr() for o in outs], None)
     assert rc == 0
     torch.cuda.synchronize()
@@ -40,6 +41,8 @@ def test_mma_selftest(cuda, corrected):
         "gram_offset": np.abs(D3[:48, :16] - E3).max(),
         "update_acc": np.abs(D4[:, :48] - E4).max(),
     }
-    print(errs)
+    if variant == 1:
+        errs = {"update_neg": errs["update_neg"]}
+    print(variant, corrected, errs)
     for k, v in errs.items():
         assert v < tol, (k, v, errs)

@@ -134,10 +134,11 @@ def test_row_sharded_virtual_ranks(cuda, oracle, P):
     mp = m // P
     slabs = [tq.to_colmajor(a_dev[p * mp:(p + 1) * mp]) for p in range(P)]
     wss = [torch.empty(lib.tsqr_b200_tsqr_workspace_bytes(mp, n), dtype=torch.uint8, device="cuda") for _ in range(P)]
-    rs = [tq.tsqr_reduce(slabs[p], "fp32_notc", wss[p]) for p in range(P)]
+    rq = [tq.tsqr_reduce(slabs[p], "fp32_notc", wss[p]) for p in range(P)]
+    rs = [x[0] for x in rq]
     stacked = tq.to_colmajor(torch.cat(rs, dim=0))
     qroot, r = tq.tsqr(stacked, "fp32_notc")
-    qs = [tq.tsqr_build(slabs[p], "fp32_notc", wss[p], b=tq.to_colmajor(qroot[p * n:(p + 1) * n])) for p in range(P)]
+    qs = [tq.tsqr_build(slabs[p], "fp32_notc", wss[p], b=tq.to_colmajor(qroot[p * n:(p + 1) * n]), q=rq[p][1]) for p in range(P)]
     torch.cuda.synchronize()
     q = torch.cat(qs, dim=0).cpu().numpy().astype(np.float64)
     _check(oracle, q, r.cpu().numpy().astype(np.float64), a.astype(np.float64), "fp32_notc", r_tol=1e-5)

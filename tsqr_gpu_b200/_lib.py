@@ -21,13 +21,13 @@ SIGNATURES = {
     "tsqr_b200_tsqr_workspace_bytes": (_sz, [_sz, _sz]),
     "tsqr_b200_qr": (_c.c_int, [_c.c_int, _c.c_int, _vp, _sz, _vp, _sz, _vp, _sz, _sz, _sz, _vp, _sz, _vp]),
     "tsqr_b200_tsqr": (_c.c_int, [_c.c_int, _vp, _sz, _vp, _sz, _vp, _sz, _sz, _sz, _vp, _sz, _vp]),
-    "tsqr_b200_tsqr_reduce": (_c.c_int, [_c.c_int, _vp, _sz, _sz, _sz, _vp, _vp, _sz, _vp]),
+    "tsqr_b200_tsqr_reduce": (_c.c_int, [_c.c_int, _vp, _sz, _sz, _sz, _vp, _vp, _sz, _vp, _sz, _vp]),
     "tsqr_b200_tsqr_build": (_c.c_int, [_c.c_int, _vp, _sz, _vp, _sz, _sz, _sz, _vp, _sz, _vp, _sz, _vp]),
     "tsqr_b200_qr32x16_batched": (_c.c_int, [_c.c_int, _vp, _sz, _vp, _sz, _vp, _sz, _c.c_uint, _c.c_uint, _sz, _vp, _vp]),
     "tsqr_b200_launch_count": (_c.c_ulonglong, []),
     "tsqr_b200_profile_enable": (None, [_c.c_int]),
     "tsqr_b200_profile_read": (_c.c_int, [_vp, _vp, _c.c_int]),
-    "tsqr_b200_selftest_mma": (_c.c_int, [_c.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "tsqr_b200_selftest_mma": (_c.c_int, [_c.c_int, _c.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 
 

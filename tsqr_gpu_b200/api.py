@@ -149,16 +149,20 @@ def tsqr(a, mode="fp32_notc", buffer=None, q=None, r=None):
     return q, r
 
 
-def tsqr_reduce(a, mode, ws):
-    """step 1 of the row-sharded TSQR: local slab -> local R (n x n float32, column-major)"""
+def tsqr_reduce(a, mode, ws, q=None):
+    """step 1 of the row-sharded TSQR: local slab -> (local R (n x n float32, column-major), q).
+    The same q must be handed to tsqr_build: the tensor-core modes keep the reflectors in it."""
     md = _mode(mode)
     m, n = a.shape
     lda = _check_colmajor(a, "a")
+    if q is None:
+        q = colmajor_empty(m, n, a.dtype, a.device)
+    ldq = _check_colmajor(q, "q")
     r_local = torch.empty((n, n), dtype=torch.float32, device=a.device).t()
-    code = lib.tsqr_b200_tsqr_reduce(md, a.data_ptr(), lda, m, n, r_local.data_ptr(), ws.data_ptr(), ws.numel(),
-                                     _stream())
+    code = lib.tsqr_b200_tsqr_reduce(md, a.data_ptr(), lda, m, n, r_local.data_ptr(), q.data_ptr(), ldq,
+                                     ws.data_ptr(), ws.numel(), _stream())
     _raise(code)
-    return r_local
+    return r_local, q
 
 
 def tsqr_build(a, mode, ws, b=None, q=None):

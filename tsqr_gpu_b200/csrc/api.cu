@@ -101,15 +101,15 @@ int tsqr_b200_tsqr(int mode, void* q, size_t ldq, void* r, size_t ldr, const voi
   });
 }
 
-int tsqr_b200_tsqr_reduce(int mode, const void* a, size_t lda, size_t m, size_t n, float* r_local, void* ws,
-                          size_t ws_bytes, void* stream) {
+int tsqr_b200_tsqr_reduce(int mode, const void* a, size_t lda, size_t m, size_t n, float* r_local, void* q, size_t ldq,
+                          void* ws, size_t ws_bytes, void* stream) {
   if (!mode_valid(mode)) { set_err("invalid compute mode"); return TSQR_B200_ERR_ARGUMENT; }
   if (m == 0 || n == 0 || n > (size_t)kMaxN) return TSQR_B200_INVALID_SIZE;
-  if (!a || !ws || !r_local) { set_err("null pointer argument"); return TSQR_B200_ERR_ARGUMENT; }
+  if (!a || !ws || !r_local || !q) { set_err("null pointer argument"); return TSQR_B200_ERR_ARGUMENT; }
   return guarded([&] {
-    Plan plan = make_plan((long long)m, (int)n);
+    Plan plan = make_plan_for(mode, (long long)m, (int)n);
     if (plan.total_floats * sizeof(float) > ws_bytes) throw std::runtime_error("tsqr_b200: workspace too small");
-    const float* r32 = tsqr_reduce(plan, mode, a, (long long)lda, (float*)ws, (cudaStream_t)stream);
+    const float* r32 = tsqr_reduce(plan, mode, a, (long long)lda, q, (long long)ldq, (float*)ws, (cudaStream_t)stream);
     store_r(r32, (int)n, r_local, (long long)n, IoType::f32, (cudaStream_t)stream);
     return 0;
   });
@@ -121,7 +121,7 @@ int tsqr_b200_tsqr_build(int mode, void* q, size_t ldq, const void* a, size_t ld
   if (m == 0 || n == 0 || n > (size_t)kMaxN) return TSQR_B200_INVALID_SIZE;
   if (!a || !ws || !q) { set_err("null pointer argument"); return TSQR_B200_ERR_ARGUMENT; }
   return guarded([&] {
-    Plan plan = make_plan((long long)m, (int)n);
+    Plan plan = make_plan_for(mode, (long long)m, (int)n);
     if (plan.total_floats * sizeof(float) > ws_bytes) throw std::runtime_error("tsqr_b200: workspace too small");
     tsqr_build(plan, mode, a, (long long)lda, q, (long long)ldq, b, (long long)ldb, (float*)ws, (cudaStream_t)stream);
     return 0;

@@ -157,7 +157,7 @@ QrWs carve(long long m, long long n, bool reorth) {
   const int nbmax = (int)std::min<long long>(n, kNB);
   size_t off = 0;
   auto take = [&](size_t f) { size_t o = off; off = (off + f + 63) / 64 * 64; return o; };
-  w.tsqr_off = take(make_plan(m, nbmax).total_floats);
+  w.tsqr_off = take(plan_floats_any(m, nbmax));
   if (n > kNB) {
     const long long kbmax = (n - 1) / kNB * kNB;
     w.nslabs = (int)std::min<long long>(2LL * device_sm_count(), (m + 1023) / 1024);
@@ -206,8 +206,8 @@ int qr_typed(int mode, bool reorth, T* q, long long ldq, T* r, long long ldr, T*
     T* A2 = a + c0 * lda;
     T* Q2 = q + c0 * ldq;
     if (kb > 0) project<T>(q, ldq, kb, A2, lda, nb, m, w, ws, ws + w.c_off, s);
-    Plan plan = make_plan(m, nb);
-    const float* r22 = tsqr_reduce(plan, mode, A2, lda, tws, s);
+    Plan plan = make_plan_for(mode, m, nb);
+    const float* r22 = tsqr_reduce(plan, mode, A2, lda, Q2, ldq, tws, s);
     if (kb > 0) copy_block<<<(kb * nb + 255) / 256, 256, 0, s>>>(ws + w.c_off, kb, Rcol, ldrc, kb, nb);
     note_launch();
     copy_block<<<(nb * nb + 255) / 256, 256, 0, s>>>(r22, nb, Rcol + kb, ldrc, nb, nb);
@@ -216,7 +216,7 @@ int qr_typed(int mode, bool reorth, T* q, long long ldq, T* r, long long ldr, T*
     if (reorth && kb > 0) {
       // second projection and second TSQR of the panel (CGS2), then fix up R
       project<T>(q, ldq, kb, Q2, ldq, nb, m, w, ws, ws + w.s_off, s);
-      const float* wfac = tsqr_reduce(plan, mode, Q2, ldq, tws, s);
+      const float* wfac = tsqr_reduce(plan, mode, Q2, ldq, Q2, ldq, tws, s);
       float* Wm = ws + w.w_off;
       float* R22old = Wm + kNB * kNB;
       copy_block<<<(nb * nb + 255) / 256, 256, 0, s>>>(wfac, nb, Wm, nb, nb, nb);

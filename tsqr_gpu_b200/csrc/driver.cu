@@ -54,7 +54,48 @@ int profile_read(int* labels, float* ms, int cap) {
 
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-Plan make_plan(long long m, int n, int max_chunks0) {
+static Plan make_plan_tc(long long m, int n, int max_chunks0) {
+  Plan plan;
+  plan.tc = true;
+  plan.m = m;
+  plan.n = n;
+  plan.np = tc_np(n);
+  const int NP = plan.np, H = kTcTileRows;
+  size_t off = 0;
+  long long rows = m;
+  int level = 0;
+  while (true) {
+    Level L{};
+    L.rows = rows;
+    long long tiles_pc;
+    if (rows <= NP + 8LL * H) {
+      tiles_pc = (rows > NP) ? (rows - NP + H - 1) / H : 0;
+    } else if (level == 0) {
+      const long long want = max_chunks0 > 0 ? max_chunks0 : 2LL * device_sm_count();  // 2 CTAs per SM
+      const long long per = (rows + want - 1) / want;
+      tiles_pc = std::max<long long>(4, (per - NP + H - 1) / H);
+    } else {
+      tiles_pc = 4;  // short chains keep the upper levels shallow in time
+    }
+    L.rows_per_chunk = NP + tiles_pc * H;
+    L.tiles_per_chunk = (int)tiles_pc;
+    L.nchunks = (int)std::max<long long>(1, (rows + L.rows_per_chunk - 1) / L.rows_per_chunk);
+    L.ckpt_off = off;
+    L.S_off = off;
+    off = align_up(off + (size_t)L.nchunks * n * n, 64);
+    L.Qup_off = off;
+    off = align_up(off + (size_t)L.nchunks * n * n, 64);
+    plan.levels.push_back(L);
+    if (L.nchunks == 1) break;
+    rows = (long long)L.nchunks * n;
+    ++level;
+  }
+  plan.total_floats = off;
+  return plan;
+}
+
+Plan make_plan(long long m, int n, int max_chunks0, bool tc) {
+  if (tc) return make_plan_tc(m, n, max_chunks0);
   Plan plan;
   plan.m = m;
   plan.n = n;
@@ -97,8 +138,28 @@ Plan make_plan(long long m, int n, int max_chunks0) {
   return plan;
 }
 
-size_t tsqr_workspace_bytes(long long m, int n) {
-  return make_plan(m, n).total_floats * sizeof(float) + 256;
+size_t plan_floats_any(long long m, int n) {
+  return std::max(make_plan(m, n, 0, false).total_floats, make_plan(m, n, 0, true).total_floats);
+}
+
+size_t tsqr_workspace_bytes(long long m, int n) { return plan_floats_any(m, n) * sizeof(float) + 256; }
+
+static TcParams tc_level_params(const Plan& plan, size_t li, const void* a, long long lda, void* q, long long ldq, float* ws) {
+  const Level& L = plan.levels[li];
+  TcParams p{};
+  p.n = plan.n;
+  p.M = L.rows;
+  p.nchunks = L.nchunks;
+  p.rows_per_chunk = L.rows_per_chunk;
+  if (li == 0) {
+    p.A = a; p.lda = lda; p.Q = q; p.ldq = ldq;
+  } else {
+    p.A = ws + plan.levels[li - 1].S_off; p.lda = L.rows;
+    p.Q = ws + plan.levels[li - 1].Qup_off; p.ldq = L.rows;
+  }
+  p.S = ws + L.S_off;
+  p.lds = (long long)L.nchunks * plan.n;
+  return p;
 }
 
 static PassParams level_params(const Plan& plan, size_t li, const void* a, long long lda, float* ws) {
@@ -123,7 +184,17 @@ static PassParams level_params(const Plan& plan, size_t li, const void* a, long 
   return p;
 }
 
-const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long lda, float* ws, cudaStream_t s) {
+const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long lda, void* q, long long ldq, float* ws,
+                         cudaStream_t s) {
+  if (plan.tc) {
+    for (size_t li = 0; li < plan.levels.size(); ++li) {
+      TcParams p = tc_level_params(plan, li, a, lda, q, ldq, ws);
+      ProfScope prof(s, (int)li * 2);
+      const IoType io = li == 0 ? mode_io(mode) : IoType::f32;
+      launch_tc_reduce(p, mode_is_cor(mode), io, io, s);
+    }
+    return ws + plan.levels.back().S_off;
+  }
   for (size_t li = 0; li < plan.levels.size(); ++li) {
     PassParams p = level_params(plan, li, a, lda, ws);
     ProfScope prof(s, (int)li * 2);
@@ -134,6 +205,17 @@ const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long ld
 
 void tsqr_build(const Plan& plan, int mode, const void* a, long long lda, void* q, long long ldq,
                 const float* B, long long ldb, float* ws, cudaStream_t s) {
+  if (plan.tc) {
+    for (size_t li = plan.levels.size(); li-- > 0;) {
+      const Level& L = plan.levels[li];
+      TcParams p = tc_level_params(plan, li, a, lda, q, ldq, ws);
+      ProfScope prof(s, (int)li * 2 + 1);
+      if (li + 1 == plan.levels.size()) { p.Bsrc = B; p.ldb = ldb; }
+      else { p.Bsrc = ws + L.Qup_off; p.ldb = (long long)L.nchunks * plan.n; }
+      launch_tc_build(p, mode_is_cor(mode), li == 0 ? mode_io(mode) : IoType::f32, s);
+    }
+    return;
+  }
   for (size_t li = plan.levels.size(); li-- > 0;) {
     const Level& L = plan.levels[li];
     PassParams p = level_params(plan, li, a, lda, ws);
@@ -177,9 +259,9 @@ void store_r(const float* r32, int n, void* r, long long ldr, IoType t, cudaStre
 
 void tsqr_full(int mode, void* q, long long ldq, void* r, long long ldr, const void* a, long long lda,
                long long m, int n, float* ws, size_t ws_bytes, cudaStream_t s) {
-  Plan plan = make_plan(m, n);
+  Plan plan = make_plan_for(mode, m, n);
   if (plan.total_floats * sizeof(float) > ws_bytes) throw std::runtime_error("tsqr_b200: workspace too small");
-  const float* r32 = tsqr_reduce(plan, mode, a, lda, ws, s);
+  const float* r32 = tsqr_reduce(plan, mode, a, lda, q, ldq, ws, s);
   store_r(r32, n, r, ldr, mode_io(mode), s);
   tsqr_build(plan, mode, a, lda, q, ldq, nullptr, 0, ws, s);
 }

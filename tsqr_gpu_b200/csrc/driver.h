@@ -30,6 +30,7 @@ struct Level {
 };
 
 struct Plan {
+  bool tc = false;  // tensor-core passes (TcParams chunk format) instead of the CUDA-core passes
   long long m;
   int n, np;
   std::vector<Level> levels;
@@ -43,12 +44,22 @@ int device_sm_count();
 void profile_enable(bool on);
 int profile_read(int* labels, float* ms, int cap);  // returns #records copied, clears them
 // levels for an m x n TSQR (n <= kMaxN). max_chunks0 <= 0 picks 1 CTA wave per SM x occupancy.
-Plan make_plan(long long m, int n, int max_chunks0 = 0);
+Plan make_plan(long long m, int n, int max_chunks0 = 0, bool tc = false);
+// the *_tc_* modes run on the tensor-core passes when the matrix is tall enough
+inline bool mode_is_tc(int m) { return m == fp16_tc_nocor || m == fp32_tc_cor || m == fp32_tc_nocor || m == tf32_tc_cor || m == tf32_tc_nocor; }
+inline bool mode_is_cor(int m) { return m == fp32_tc_cor || m == tf32_tc_cor; }
+constexpr long long kTcMinRows = 1024;
+inline bool use_tc(int mode, long long m) { return mode_is_tc(mode) && m >= kTcMinRows; }
+inline Plan make_plan_for(int mode, long long m, int n) { return make_plan(m, n, 0, use_tc(mode, m)); }
+// workspace floats that cover every mode's plan
+size_t plan_floats_any(long long m, int n);
 size_t tsqr_workspace_bytes(long long m, int n);
 
 // A (m x n) -> R_local (n x n fp32, column-major ld n, upper triangular, inside the
 // workspace at the returned pointer) and the checkpoints needed by tsqr_build.
-const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long lda, float* ws, cudaStream_t s);
+// The tensor-core plan also writes the reflector tails into q (same shape as a; q may alias a).
+const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long lda, void* q, long long ldq, float* ws,
+                         cudaStream_t s);
 // Q = Q_local * B, with B (n x n fp32, column-major ldb) or identity when B == nullptr.
 void tsqr_build(const Plan& plan, int mode, const void* a, long long lda, void* q, long long ldq,
                 const float* B, long long ldb, float* ws, cudaStream_t s);

@@ -49,13 +49,14 @@ __device__ __forceinline__ void tile_store(char* hi, char* lo, uint32_t off, flo
 
 // ---- descriptors
 // shared-memory matrix descriptor, SWIZZLE_128B, version 1 (Blackwell)
-__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                             uint32_t layout_type = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((addr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;  // descriptor version
-  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  d |= (uint64_t)layout_type << 61;  // 0 = no swizzle, 2 = SWIZZLE_128B
   return d;
 }
 
@@ -135,6 +136,23 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) 
       "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15]))
       : "memory");
 }
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
+  uint32_t r[8];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const float (&v)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr),
+               "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])),
+               "r"(__float_as_uint(v[3])), "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])),
+               "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7]))
+               : "memory");
+}
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 // TMEM address of (lane base of this warp, column)
@@ -190,6 +208,134 @@ __device__ __forceinline__ void update_issue(uint32_t d_tmem, uint32_t a_hi, uin
     }
   }
 }
+
+// =========================================================================================
+// "ns" tile buffer: NO-swizzle canonical layout with a padded core-matrix stride. Core matrix =
+// 8 columns x 4 rows (8 x 16 bytes, contiguous 128 B):
+//     off(row, col) = (col/8)*SB + (row/4)*144 + (col%8)*16 + (row%4)*4,   SB = (rows/4)*144
+// K-major view (K = rows, MN = cols): LBO = 144, SBO = SB. MN-major view (MN = rows, K = cols):
+// SBO = 144, LBO = SB. The 144-byte stride makes thread-per-row scalar stores conflict free.
+namespace ns {
+constexpr uint32_t kCM = 144;
+__host__ __device__ constexpr uint32_t sb(int rows) { return (uint32_t)(rows / 4) * kCM; }
+__host__ __device__ constexpr uint32_t bytes(int rows, int cols) { return (uint32_t)(cols / 8) * sb(rows); }
+__device__ __forceinline__ uint32_t off(int row, int col, int rows) {
+  return (uint32_t)(col >> 3) * sb(rows) + (uint32_t)(row >> 2) * kCM + (uint32_t)((col & 7) << 4) + (uint32_t)((row & 3) << 2);
+}
+// D[128 x N] (+)= A[:, a_c0 + m]^T B[:, b_c0 + n] over rows [0, krows)
+template <bool COR>
+__device__ __forceinline__ void gram_issue(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_rows, int a_c0,
+                                           uint32_t b_hi, uint32_t b_lo, int b_rows, int b_c0, int N, int krows,
+                                           bool accumulate) {
+  const uint32_t id = idesc_tf32(128, N, false, false, false);
+  const uint32_t asb = sb(a_rows), bsb = sb(b_rows);
+  const uint32_t a0 = (uint32_t)(a_c0 >> 3) * asb, b0 = (uint32_t)(b_c0 >> 3) * bsb;
+  bool acc = accumulate;
+  for (int k = 0; k < krows; k += 8) {
+    const uint32_t ko = (uint32_t)(k >> 2) * kCM;
+    const uint64_t ah = smem_desc(a_hi + a0 + ko, kCM, asb, 0), bh = smem_desc(b_hi + b0 + ko, kCM, bsb, 0);
+    mma_tf32(d_tmem, ah, bh, id, acc);
+    acc = true;
+    if (COR) {
+      mma_tf32(d_tmem, ah, smem_desc(b_lo + b0 + ko, kCM, bsb, 0), id, true);
+      mma_tf32(d_tmem, smem_desc(a_lo + a0 + ko, kCM, asb, 0), bh, id, true);
+    }
+  }
+}
+// D[128 rows x N] (+)= (neg ? -1 : 1) * A[:, a_c0 : a_c0+kcols] * B[b_k0 : b_k0+kcols, b_c0 : b_c0+N]
+// A: 128-row ns buffer (MN-major view); B: ns buffer with b_rows rows (K-major view, K = its rows)
+template <bool COR>
+__device__ __forceinline__ void update_issue(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_c0, uint32_t b_hi,
+                                             uint32_t b_lo, int b_rows, int b_c0, int b_k0, int N, int kcols, bool neg,
+                                             bool accumulate) {
+  const uint32_t id = idesc_tf32(128, N, true, false, neg);
+  const uint32_t asb = sb(128), bsb = sb(b_rows);
+  bool acc = accumulate;
+  for (int k = 0; k < kcols; k += 8) {
+    const uint32_t ao = (uint32_t)((a_c0 + k) >> 3) * asb;
+    const uint32_t bo = (uint32_t)(b_c0 >> 3) * bsb + (uint32_t)((b_k0 + k) >> 2) * kCM;
+    const uint64_t ah = smem_desc(a_hi + ao, asb, kCM, 0), bh = smem_desc(b_hi + bo, kCM, bsb, 0);
+    mma_tf32(d_tmem, ah, bh, id, acc);
+    acc = true;
+    if (COR) {
+      mma_tf32(d_tmem, ah, smem_desc(b_lo + bo, kCM, bsb, 0), id, true);
+      mma_tf32(d_tmem, smem_desc(a_lo + ao, asb, kCM, 0), bh, id, true);
+    }
+  }
+}
+}  // namespace ns
+
+// "rn" buffer: 128 rows x cols stored row-wise without swizzle, a K-major operand with K = columns.
+// Core matrix = 8 rows x 4 columns: off(row, col) = (col/4)*2048 + (row/8)*128 + (row%8)*16 + (col%4)*4
+// (LBO = 2048 between K core matrices, SBO = 128 between 8-row groups). A thread that owns a row
+// stores 4 consecutive columns as one float4; 8 consecutive lanes fill one 128-byte core matrix.
+namespace rn {
+__host__ __device__ constexpr uint32_t bytes(int cols) { return (uint32_t)cols * 512u; }
+__device__ __forceinline__ uint32_t off4(int row, int col4) {  // col4 = col / 4
+  return (uint32_t)col4 * 2048u + (uint32_t)(row >> 3) * 128u + (uint32_t)((row & 7) << 4);
+}
+template <bool COR>
+__device__ __forceinline__ void store4(char* hi, char* lo, int row, int col4, float x0, float x1, float x2, float x3) {
+  const uint32_t o = off4(row, col4);
+  const float4 h = make_float4(to_tf32_rna(x0), to_tf32_rna(x1), to_tf32_rna(x2), to_tf32_rna(x3));
+  *reinterpret_cast<float4*>(hi + o) = h;
+  if (COR) *reinterpret_cast<float4*>(lo + o) = make_float4(__fsub_rn(x0, h.x), __fsub_rn(x1, h.y), __fsub_rn(x2, h.z), __fsub_rn(x3, h.w));
+}
+// D[128 rows x N] (+)= (neg ? -1 : 1) * A[:, a_c0 : a_c0+kcols] * B[b_k0 : b_k0+kcols, b_c0 : b_c0+N]
+// A: rn buffer; B: ns buffer with b_rows rows (K-major view, K = its rows)
+template <bool COR>
+__device__ __forceinline__ void update_issue(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_c0, uint32_t b_hi,
+                                             uint32_t b_lo, int b_rows, int b_c0, int b_k0, int N, int kcols, bool neg,
+                                             bool accumulate) {
+  const uint32_t id = idesc_tf32(128, N, false, false, neg);
+  const uint32_t bsb = ns::sb(b_rows);
+  bool acc = accumulate;
+  for (int k = 0; k < kcols; k += 8) {
+    const uint32_t ao = (uint32_t)((a_c0 + k) >> 2) * 2048u;
+    const uint32_t bo = (uint32_t)(b_c0 >> 3) * bsb + (uint32_t)((b_k0 + k) >> 2) * ns::kCM;
+    const uint64_t ah = smem_desc(a_hi + ao, 2048, 128, 0), bh = smem_desc(b_hi + bo, ns::kCM, bsb, 0);
+    mma_tf32(d_tmem, ah, bh, id, acc);
+    acc = true;
+    if (COR) {
+      mma_tf32(d_tmem, ah, smem_desc(b_lo + bo, ns::kCM, bsb, 0), id, true);
+      mma_tf32(d_tmem, smem_desc(a_lo + ao, 2048, 128, 0), bh, id, true);
+    }
+  }
+}
+}  // namespace rn
+
+// "rk" buffer: 128 rows x cols (multiple of 32) stored row-wise for use as a K-major A operand
+// with K = columns (SWIZZLE_128B): off = (col/32)*16384 + (row/8)*1024 + (row%8)*128
+//                                        + ((((col%32)/4) ^ (row%8)) * 16) + (col%4)*4
+namespace rk {
+__device__ __forceinline__ uint32_t off(int row, int col) {
+  const int c32 = col & 31, r8 = row & 7;
+  return (uint32_t)(col >> 5) * 16384u + (uint32_t)(row >> 3) * 1024u + (uint32_t)(r8 << 7) +
+         (uint32_t)((((c32 >> 2) ^ r8)) << 4) + (uint32_t)((c32 & 3) << 2);
+}
+// D[128 x N] (+)= +-A[:, a_c0 : a_c0+kcols] * B, B in the SWIZZLE_128B column tile buffer (tile_off)
+template <bool COR>
+__device__ __forceinline__ void update_issue(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_c0, uint32_t b_hi,
+                                             uint32_t b_lo, int b_cols, int b_c0, int b_k0, int N, int kcols, bool neg,
+                                             bool accumulate) {
+  const uint32_t id = idesc_tf32(128, N, false, false, neg);
+  const uint32_t b_rb = (uint32_t)(b_cols >> 3) << 10;
+  bool acc = accumulate;
+  for (int k = 0; k < kcols; k += 8) {
+    const int ac = a_c0 + k;
+    const uint32_t ao = (uint32_t)(ac >> 5) * 16384u + (uint32_t)(ac & 31) * 4;
+    const int bk = b_k0 + k;
+    const uint32_t bo = ((uint32_t)(b_c0 >> 3) << 10) + (uint32_t)(bk >> 5) * b_rb + (uint32_t)(bk & 31) * 4;
+    const uint64_t ah = smem_desc(a_hi + ao, 16, 1024), bh = smem_desc(b_hi + bo, 16, 1024);
+    mma_tf32(d_tmem, ah, bh, id, acc);
+    acc = true;
+    if (COR) {
+      mma_tf32(d_tmem, ah, smem_desc(b_lo + bo, 16, 1024), id, true);
+      mma_tf32(d_tmem, smem_desc(a_lo + ao, 16, 1024), bh, id, true);
+    }
+  }
+}
+}  // namespace rk
 
 }  // namespace tc
 }  // namespace tsqr_b200

@@ -55,4 +55,35 @@ inline size_t ckpt_floats(int np) { return (size_t)np * (np + 1) / 2; }
 void launch_pass_simt(const PassParams& p, bool build, IoType in, IoType out, cudaStream_t s);
 int pass_simt_max_ctas_per_sm(int np, bool build);
 
+
+// ---------------------------------------------------------------------------------------------
+// Tensor-core (tcgen05 / TMEM) level passes, used by every *_tc_* compute mode.
+//
+// A chunk of rows [cbeg, cend) is: a HEAD block (its first NP rows, plain Householder QR) that
+// seeds the running R, followed by 128-row TILES reduced one after the other as [R ; A_tile]
+// with structured reflectors [e_j ; v_j] (flat tree).
+//   reduce: A -> R per chunk (stacked into S) and the reflector tails V, written into the Q
+//           buffer at the rows they belong to (head: strictly lower part of V0).
+//   build : walks a chunk's tiles in reverse; per tile S = V^T V (tensor cores), solves
+//           T^-1 X = B with T^-1 = striu(S) + diag((1+S_jj)/2), Q_tile = -V X (tensor cores),
+//           B <- B - X; finally Q_head = H_0 .. H_{NP-1} B. Q overwrites V in place.
+struct TcParams {
+  const void* A;
+  long long lda;
+  long long M;               // rows of the level input
+  int n;                     // true column count (<= NP)
+  int nchunks;
+  long long rows_per_chunk;  // the last chunk takes every remaining row
+  void* Q;                   // V (reduce: out, build: in) then Q (build: out)
+  long long ldq;
+  float* S;                  // reduce: stacked R, (nchunks*n) x n column-major
+  long long lds;
+  const float* Bsrc;         // build: parent Q, chunk c uses rows [c*n, c*n+n); nullptr => identity
+  long long ldb;
+};
+constexpr int kTcTileRows = 128;
+inline int tc_np(int n) { return n <= 16 ? 16 : (n <= 32 ? 32 : 64); }
+void launch_tc_reduce(const TcParams& p, bool corrected, IoType in, IoType q, cudaStream_t s);
+void launch_tc_build(const TcParams& p, bool corrected, IoType q, cudaStream_t s);
+
 }  // namespace tsqr_b200

@@ -27,7 +27,7 @@ def tsqr_sharded(a_local, mode, ws, group=None, q=None, world_size=None, rank=No
     n = a_local.shape[1]
     P = dist.get_world_size(group) if world_size is None else world_size
     p = dist.get_rank(group) if rank is None else rank
-    r_local = api.tsqr_reduce(a_local, mode, ws)                     # (n, n) column-major float32
+    r_local, q = api.tsqr_reduce(a_local, mode, ws, q=q)             # (n, n) column-major float32
     if P == 1:
         gathered = r_local.t().contiguous().view(1, n, n)
     else:
