@@ -41,8 +41,8 @@ def test_mma_selftest(cuda, corrected, variant):
         "gram_offset": np.abs(D3[:48, :16] - E3).max(),
         "update_acc": np.abs(D4[:, :48] - E4).max(),
     }
-    if variant == 1:
-        errs = {"update_neg": errs["update_neg"]}
+    keep = ("gram", "gram_offset") if variant == 0 else ("update_neg", "update_acc")
+    errs = {k: errs[k] for k in keep}
     print(variant, corrected, errs)
     for k, v in errs.items():
         assert v < tol, (k, v, errs)

@@ -1,16 +1,11 @@
 // tcgen05 / TMEM / mbarrier primitives for sm_100a, hand-written PTX (no CUTLASS on the path).
 //
-// Operand staging convention used by every tensor-core kernel of the library ("tile buffer"):
-// a rows x cols fp32 (tf32 container) matrix is kept in shared memory in the 128-byte-swizzled
-// UMMA canonical layout, cut into 1 KiB atoms of 32 rows x 8 columns:
-//
-//     atom(rb, cg)  at  (rb * (cols/8) + cg) * 1024 bytes          rb = row/32, cg = col/8
-//     inside an atom: (col%8)*128 + ((((row%32)/4) ^ (col%8)) * 16) + (row%4)*4
-//
-// The same bytes are a valid K-major operand with K = rows (MN = columns: used for the Gram
-// products V^T A, V^T V) and a valid MN-major operand with MN = rows (K = columns: used for the
-// updates A -= V W and Q = V X), so a reflector block is written once and used in both roles.
-// A warp that writes 32 consecutive rows of one column touches 32 distinct banks.
+// Operand staging: every tensor-core operand is an fp32 (tf32 container) matrix in shared memory in
+// the UMMA canonical NO-swizzle K-major layout (core matrix = 8 x 16 bytes), in one of two forms:
+//   "ns": column-wise, K = rows    -> Gram products (V^T A, V^T V) and the small B operands (W, X)
+//   "rn": row-wise,    K = columns -> the A operand of the updates (A -= V W, Q = -V X)
+// kind::tf32 has no usable MN-major form for these buffers (measured: such MMAs leave the
+// accumulator untouched), so a reflector block is stored once in each form.
 //
 // hi/lo error correction: hi = tf32(x) rounded to nearest (cvt.rna), lo = x - hi (exact in
 // fp32, read by the tensor core as tf32). A corrected product is three MMAs into one fp32
@@ -25,12 +20,6 @@ namespace tc {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
-}
-
-// ---- tile buffer addressing (byte offset of element (row, col); cols = buffer width, multiple of 8)
-__device__ __forceinline__ uint32_t tile_off(int row, int col, int cols) {
-  const int rb = row >> 5, cg = col >> 3, c8 = col & 7, r32 = row & 31;
-  return (uint32_t)(((rb * (cols >> 3) + cg) << 10) + (c8 << 7) + ((((r32 >> 2) ^ c8)) << 4) + ((r32 & 3) << 2));
 }
 
 __device__ __forceinline__ float to_tf32_rna(float x) {
@@ -48,9 +37,9 @@ __device__ __forceinline__ void tile_store(char* hi, char* lo, uint32_t off, flo
 }
 
 // ---- descriptors
-// shared-memory matrix descriptor, SWIZZLE_128B, version 1 (Blackwell)
+// shared-memory matrix descriptor, version 1 (Blackwell); layout_type 0 = no swizzle
 __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
-                                             uint32_t layout_type = 2) {
+                                             uint32_t layout_type = 0) {
   uint64_t d = 0;
   d |= (uint64_t)((addr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
@@ -95,6 +84,8 @@ __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
 }
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // ---- fences
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
@@ -160,55 +151,6 @@ __device__ __forceinline__ uint32_t tmem_addr(uint32_t base, int warp, int col) 
   return base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)col;
 }
 
-// ---- composite products on tile buffers (issued by ONE thread) ---------------------------
-// D[M=128 x N] (+)= sum over K = rows [0, krows) of  Acols^T * Bcols   (both K-major views)
-//   A buffer: a_cols wide, M index = column a_c0 + m (reads 128 columns: whatever lies behind
-//   the real ones only produces accumulator rows nobody reads); B buffer: b_cols wide, N
-//   index = column b_c0 + n. krows multiple of 8.
-template <bool COR>
-__device__ __forceinline__ void gram_issue(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_cols, int a_c0,
-                                           uint32_t b_hi, uint32_t b_lo, int b_cols, int b_c0, int N, int krows,
-                                           bool accumulate) {
-  const uint32_t id = idesc_tf32(128, N, false, false, false);
-  const uint32_t a_rb = (uint32_t)(a_cols >> 3) << 10, b_rb = (uint32_t)(b_cols >> 3) << 10;
-  const uint32_t a0 = (uint32_t)(a_c0 >> 3) << 10, b0 = (uint32_t)(b_c0 >> 3) << 10;
-  bool acc = accumulate;
-  for (int k = 0; k < krows; k += 8) {
-    const uint32_t ao = a0 + (uint32_t)(k >> 5) * a_rb + (uint32_t)(k & 31) * 4;
-    const uint32_t bo = b0 + (uint32_t)(k >> 5) * b_rb + (uint32_t)(k & 31) * 4;
-    mma_tf32(d_tmem, smem_desc(a_hi + ao, 16, 1024), smem_desc(b_hi + bo, 16, 1024), id, acc);
-    acc = true;
-    if (COR) {
-      mma_tf32(d_tmem, smem_desc(a_hi + ao, 16, 1024), smem_desc(b_lo + bo, 16, 1024), id, true);
-      mma_tf32(d_tmem, smem_desc(a_lo + ao, 16, 1024), smem_desc(b_hi + bo, 16, 1024), id, true);
-    }
-  }
-}
-
-// D[M=128 rows x N] (+)= (neg ? -1 : 1) * A[:, a_c0 : a_c0+kcols] * B     (A: MN-major view of a
-//   128-row tile buffer a_cols wide; B: K-major view of a buffer whose ROWS are the K index
-//   (kcols of them, starting at row b_k0) and whose columns are the N index from b_c0.
-template <bool COR>
-__device__ __forceinline__ void update_issue(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_cols, int a_c0,
-                                             uint32_t b_hi, uint32_t b_lo, int b_cols, int b_c0, int b_k0, int N,
-                                             int kcols, bool neg, bool accumulate) {
-  const uint32_t id = idesc_tf32(128, N, true, false, neg);
-  const uint32_t a_lbo = (uint32_t)(a_cols >> 3) << 10;  // next 32 rows
-  const uint32_t b_rb = (uint32_t)(b_cols >> 3) << 10;
-  bool acc = accumulate;
-  for (int k = 0; k < kcols; k += 8) {
-    const uint32_t ao = (uint32_t)((a_c0 + k) >> 3) << 10;
-    const int bk = b_k0 + k;
-    const uint32_t bo = ((uint32_t)(b_c0 >> 3) << 10) + (uint32_t)(bk >> 5) * b_rb + (uint32_t)(bk & 31) * 4;
-    mma_tf32(d_tmem, smem_desc(a_hi + ao, a_lbo, 1024), smem_desc(b_hi + bo, 16, 1024), id, acc);
-    acc = true;
-    if (COR) {
-      mma_tf32(d_tmem, smem_desc(a_hi + ao, a_lbo, 1024), smem_desc(b_lo + bo, 16, 1024), id, true);
-      mma_tf32(d_tmem, smem_desc(a_lo + ao, a_lbo, 1024), smem_desc(b_hi + bo, 16, 1024), id, true);
-    }
-  }
-}
-
 // =========================================================================================
 // "ns" tile buffer: NO-swizzle canonical layout with a padded core-matrix stride. Core matrix =
 // 8 columns x 4 rows (8 x 16 bytes, contiguous 128 B):
@@ -222,6 +164,8 @@ __host__ __device__ constexpr uint32_t bytes(int rows, int cols) { return (uint3
 __device__ __forceinline__ uint32_t off(int row, int col, int rows) {
   return (uint32_t)(col >> 3) * sb(rows) + (uint32_t)(row >> 2) * kCM + (uint32_t)((col & 7) << 4) + (uint32_t)((row & 3) << 2);
 }
+// column part of off(): off(row, col, rows) = off(row, 0, rows) + coloff(col, rows)
+__host__ __device__ constexpr uint32_t coloff(int col, int rows) { return (uint32_t)(col >> 3) * sb(rows) + (uint32_t)((col & 7) << 4); }
 // D[128 x N] (+)= A[:, a_c0 + m]^T B[:, b_c0 + n] over rows [0, krows)
 template <bool COR>
 __device__ __forceinline__ void gram_issue(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_rows, int a_c0,
@@ -230,37 +174,21 @@ __device__ __forceinline__ void gram_issue(uint32_t d_tmem, uint32_t a_hi, uint3
   const uint32_t id = idesc_tf32(128, N, false, false, false);
   const uint32_t asb = sb(a_rows), bsb = sb(b_rows);
   const uint32_t a0 = (uint32_t)(a_c0 >> 3) * asb, b0 = (uint32_t)(b_c0 >> 3) * bsb;
+  // the start-address field is the low 14 bits (16-byte units): one K step of 8 rows = 2 core matrices
+  uint64_t ah = smem_desc(a_hi + a0, kCM, asb), bh = smem_desc(b_hi + b0, kCM, bsb);
+  uint64_t al = COR ? smem_desc(a_lo + a0, kCM, asb) : 0, bl = COR ? smem_desc(b_lo + b0, kCM, bsb) : 0;
+  constexpr uint64_t kStep = (2 * kCM) >> 4;
   bool acc = accumulate;
+#pragma unroll 4
   for (int k = 0; k < krows; k += 8) {
-    const uint32_t ko = (uint32_t)(k >> 2) * kCM;
-    const uint64_t ah = smem_desc(a_hi + a0 + ko, kCM, asb, 0), bh = smem_desc(b_hi + b0 + ko, kCM, bsb, 0);
     mma_tf32(d_tmem, ah, bh, id, acc);
     acc = true;
     if (COR) {
-      mma_tf32(d_tmem, ah, smem_desc(b_lo + b0 + ko, kCM, bsb, 0), id, true);
-      mma_tf32(d_tmem, smem_desc(a_lo + a0 + ko, kCM, asb, 0), bh, id, true);
+      mma_tf32(d_tmem, ah, bl, id, true);
+      mma_tf32(d_tmem, al, bh, id, true);
+      al += kStep; bl += kStep;
     }
-  }
-}
-// D[128 rows x N] (+)= (neg ? -1 : 1) * A[:, a_c0 : a_c0+kcols] * B[b_k0 : b_k0+kcols, b_c0 : b_c0+N]
-// A: 128-row ns buffer (MN-major view); B: ns buffer with b_rows rows (K-major view, K = its rows)
-template <bool COR>
-__device__ __forceinline__ void update_issue(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_c0, uint32_t b_hi,
-                                             uint32_t b_lo, int b_rows, int b_c0, int b_k0, int N, int kcols, bool neg,
-                                             bool accumulate) {
-  const uint32_t id = idesc_tf32(128, N, true, false, neg);
-  const uint32_t asb = sb(128), bsb = sb(b_rows);
-  bool acc = accumulate;
-  for (int k = 0; k < kcols; k += 8) {
-    const uint32_t ao = (uint32_t)((a_c0 + k) >> 3) * asb;
-    const uint32_t bo = (uint32_t)(b_c0 >> 3) * bsb + (uint32_t)((b_k0 + k) >> 2) * kCM;
-    const uint64_t ah = smem_desc(a_hi + ao, asb, kCM, 0), bh = smem_desc(b_hi + bo, kCM, bsb, 0);
-    mma_tf32(d_tmem, ah, bh, id, acc);
-    acc = true;
-    if (COR) {
-      mma_tf32(d_tmem, ah, smem_desc(b_lo + bo, kCM, bsb, 0), id, true);
-      mma_tf32(d_tmem, smem_desc(a_lo + ao, asb, kCM, 0), bh, id, true);
-    }
+    ah += kStep; bh += kStep;
   }
 }
 }  // namespace ns
@@ -289,53 +217,26 @@ __device__ __forceinline__ void update_issue(uint32_t d_tmem, uint32_t a_hi, uin
                                              bool accumulate) {
   const uint32_t id = idesc_tf32(128, N, false, false, neg);
   const uint32_t bsb = ns::sb(b_rows);
+  const uint32_t ao = (uint32_t)(a_c0 >> 2) * 2048u;
+  const uint32_t bo = (uint32_t)(b_c0 >> 3) * bsb + (uint32_t)(b_k0 >> 2) * ns::kCM;
+  uint64_t ah = smem_desc(a_hi + ao, 2048, 128), bh = smem_desc(b_hi + bo, ns::kCM, bsb);
+  uint64_t al = COR ? smem_desc(a_lo + ao, 2048, 128) : 0, bl = COR ? smem_desc(b_lo + bo, ns::kCM, bsb) : 0;
+  constexpr uint64_t kStepA = 4096 >> 4, kStepB = (2 * ns::kCM) >> 4;
   bool acc = accumulate;
+#pragma unroll 2
   for (int k = 0; k < kcols; k += 8) {
-    const uint32_t ao = (uint32_t)((a_c0 + k) >> 2) * 2048u;
-    const uint32_t bo = (uint32_t)(b_c0 >> 3) * bsb + (uint32_t)((b_k0 + k) >> 2) * ns::kCM;
-    const uint64_t ah = smem_desc(a_hi + ao, 2048, 128, 0), bh = smem_desc(b_hi + bo, ns::kCM, bsb, 0);
     mma_tf32(d_tmem, ah, bh, id, acc);
     acc = true;
     if (COR) {
-      mma_tf32(d_tmem, ah, smem_desc(b_lo + bo, ns::kCM, bsb, 0), id, true);
-      mma_tf32(d_tmem, smem_desc(a_lo + ao, 2048, 128, 0), bh, id, true);
+      mma_tf32(d_tmem, ah, bl, id, true);
+      mma_tf32(d_tmem, al, bh, id, true);
+      al += kStepA; bl += kStepB;
     }
+    ah += kStepA; bh += kStepB;
   }
 }
 }  // namespace rn
 
-// "rk" buffer: 128 rows x cols (multiple of 32) stored row-wise for use as a K-major A operand
-// with K = columns (SWIZZLE_128B): off = (col/32)*16384 + (row/8)*1024 + (row%8)*128
-//                                        + ((((col%32)/4) ^ (row%8)) * 16) + (col%4)*4
-namespace rk {
-__device__ __forceinline__ uint32_t off(int row, int col) {
-  const int c32 = col & 31, r8 = row & 7;
-  return (uint32_t)(col >> 5) * 16384u + (uint32_t)(row >> 3) * 1024u + (uint32_t)(r8 << 7) +
-         (uint32_t)((((c32 >> 2) ^ r8)) << 4) + (uint32_t)((c32 & 3) << 2);
-}
-// D[128 x N] (+)= +-A[:, a_c0 : a_c0+kcols] * B, B in the SWIZZLE_128B column tile buffer (tile_off)
-template <bool COR>
-__device__ __forceinline__ void update_issue(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_c0, uint32_t b_hi,
-                                             uint32_t b_lo, int b_cols, int b_c0, int b_k0, int N, int kcols, bool neg,
-                                             bool accumulate) {
-  const uint32_t id = idesc_tf32(128, N, false, false, neg);
-  const uint32_t b_rb = (uint32_t)(b_cols >> 3) << 10;
-  bool acc = accumulate;
-  for (int k = 0; k < kcols; k += 8) {
-    const int ac = a_c0 + k;
-    const uint32_t ao = (uint32_t)(ac >> 5) * 16384u + (uint32_t)(ac & 31) * 4;
-    const int bk = b_k0 + k;
-    const uint32_t bo = ((uint32_t)(b_c0 >> 3) << 10) + (uint32_t)(bk >> 5) * b_rb + (uint32_t)(bk & 31) * 4;
-    const uint64_t ah = smem_desc(a_hi + ao, 16, 1024), bh = smem_desc(b_hi + bo, 16, 1024);
-    mma_tf32(d_tmem, ah, bh, id, acc);
-    acc = true;
-    if (COR) {
-      mma_tf32(d_tmem, ah, smem_desc(b_lo + bo, 16, 1024), id, true);
-      mma_tf32(d_tmem, smem_desc(a_lo + ao, 16, 1024), bh, id, true);
-    }
-  }
-}
-}  // namespace rk
 
 }  // namespace tc
 }  // namespace tsqr_b200

@@ -24,15 +24,23 @@ constexpr int kPS = 132;         // panel buffer column stride (floats), 16 B al
 constexpr unsigned kFull = 0xffffffffu;
 
 struct HhScal { float beta, tau, rden; };
-// Householder scalars for pivot alpha and tail norm^2 g: reflector [1 ; x * rden], R_jj = beta.
-// A zero column gives v = 0, tau = 2 (= 2 / (1 + |v|^2), the rule the build pass uses).
+// Householder scalars for pivot alpha and tail norm^2 g: reflector [1 ; x * rden], R_jj = beta,
+// tau = (beta - alpha) / beta = 1 + |alpha| / norm. A zero column gives v = 0, tau = 2
+// (= 2 / (1 + |v|^2), the rule the build pass uses). sqrt = rsqrt.approx + one Newton step
+// (correctly rounded to within 1 ulp), reciprocals = rcp.approx (1 ulp): the reflectors are
+// stored, never recomputed, so no bit-reproducibility is needed here.
+__device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rsqrt_approx(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ HhScal hh_scalars(float alpha, float g) {
   HhScal h;
   const float nx2 = __fmaf_rn(alpha, alpha, g);
-  if (nx2 > 0.f) {
-    h.beta = -copysignf(__fsqrt_rn(nx2), alpha);
-    h.rden = __frcp_rn(__fsub_rn(alpha, h.beta));
-    h.tau = __fdiv_rn(__fsub_rn(h.beta, alpha), h.beta);
+  if (nx2 > 1e-36f) {
+    const float y = rsqrt_approx(nx2);
+    const float n0 = __fmul_rn(nx2, y);
+    const float norm = __fmaf_rn(__fmul_rn(0.5f, y), __fmaf_rn(-n0, n0, nx2), n0);
+    h.beta = -copysignf(norm, alpha);
+    h.rden = rcp_approx(__fsub_rn(alpha, h.beta));
+    h.tau = __fmaf_rn(fabsf(alpha), rcp_approx(norm), 1.f);
   } else {
     h.beta = 0.f; h.rden = 0.f; h.tau = 2.f;
   }
@@ -62,10 +70,14 @@ static_assert(rAtHi >= 2 * ns::sb(128), "virtual column 0 of the trailing buffer
 static_assert(rAtLo - 2 * ns::sb(128) + 15 * ns::sb(128) + 31 * ns::kCM + 128 <= kReduceSmem, "Gram over-read leaves the CTA");
 
 // One 16-column panel sweep of [R_diag ; panel]. Thread (c = t%16, s = t/16) owns rows
-// [16s, 16s+16) of panel column c in registers.
-__device__ __forceinline__ void sweep16(float* Pbuf, const float* Rd, float* Rn, float* Sp, float* tau, float* part, int t) {
+// [16s, 16s+16) of panel column c in registers. Columns stay UNSCALED (x_j, not v_j = x_j * rden_j):
+// rdenv[j] is applied when the reflector block is written out, off the critical path.
+// Out: Rn (new diagonal block of R), Sp[i*16+l] = v_i . v_l (i < l), tau, rdenv.
+__device__ __forceinline__ void sweep16(float* Pbuf, const float* Rd, float* Rn, float* Sp, float* tau, float* rdenv,
+                                        float* part, int t) {
   const int c = t & 15, s = t >> 4, lane = t & 31, warp = t >> 5;
   float a[16];
+  float my_rden = 0.f;
   {
     const float4* src = reinterpret_cast<const float4*>(Pbuf + c * kPS + 16 * s);
 #pragma unroll
@@ -80,10 +92,15 @@ __device__ __forceinline__ void sweep16(float* Pbuf, const float* Rd, float* Rn,
 #pragma unroll
       for (int i = 0; i < 4; ++i) { const float4 v = src[i]; vj[4 * i] = v.x; vj[4 * i + 1] = v.y; vj[4 * i + 2] = v.z; vj[4 * i + 3] = v.w; }
     }
-    float p0 = 0.f, p1 = 0.f;
+    const float alpha = Rd[j * 17 + j];
+    const float rjc = Rd[j * 17 + c];
+    float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
 #pragma unroll
-    for (int i = 0; i < 16; i += 2) { p0 = __fmaf_rn(vj[i], a[i], p0); p1 = __fmaf_rn(vj[i + 1], a[i + 1], p1); }
-    float p = __fadd_rn(p0, p1);
+    for (int i = 0; i < 16; i += 4) {
+      p0 = __fmaf_rn(vj[i], a[i], p0); p1 = __fmaf_rn(vj[i + 1], a[i + 1], p1);
+      p2 = __fmaf_rn(vj[i + 2], a[i + 2], p2); p3 = __fmaf_rn(vj[i + 3], a[i + 3], p3);
+    }
+    float p = __fadd_rn(__fadd_rn(p0, p1), __fadd_rn(p2, p3));
     p = __fadd_rn(p, __shfl_xor_sync(kFull, p, 16));
     float* pb = part + (j & 1) * 64;
     if (lane < 16) pb[c * 4 + warp] = p;
@@ -92,28 +109,23 @@ __device__ __forceinline__ void sweep16(float* Pbuf, const float* Rd, float* Rn,
     const float4 gj4 = *reinterpret_cast<const float4*>(pb + j * 4);
     const float gc = __fadd_rn(__fadd_rn(gc4.x, gc4.y), __fadd_rn(gc4.z, gc4.w));
     const float gj = __fadd_rn(__fadd_rn(gj4.x, gj4.y), __fadd_rn(gj4.z, gj4.w));
-    const HhScal h = hh_scalars(Rd[j * 17 + j], gj);
+    const HhScal h = hh_scalars(alpha, gj);
     if (c > j) {
-      const float rjc = Rd[j * 17 + c];
       const float coef = __fmul_rn(h.tau, __fmaf_rn(gc, h.rden, rjc));
       const float cv = __fmul_rn(coef, h.rden);
 #pragma unroll
       for (int i = 0; i < 16; ++i) a[i] = __fmaf_rn(-cv, vj[i], a[i]);
-      if (s == 0) Rn[j * 17 + c] = __fsub_rn(rjc, coef);
       if (c == j + 1) {
         float4* dst = reinterpret_cast<float4*>(Pbuf + c * kPS + 16 * s);
 #pragma unroll
         for (int i = 0; i < 4; ++i) dst[i] = make_float4(a[4 * i], a[4 * i + 1], a[4 * i + 2], a[4 * i + 3]);
       }
+      if (s == 0) Rn[j * 17 + c] = __fsub_rn(rjc, coef);
     } else if (c == j) {
-#pragma unroll
-      for (int i = 0; i < 16; ++i) a[i] = __fmul_rn(vj[i], h.rden);
-      float4* dst = reinterpret_cast<float4*>(Pbuf + c * kPS + 16 * s);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) dst[i] = make_float4(a[4 * i], a[4 * i + 1], a[4 * i + 2], a[4 * i + 3]);
-      if (s == 0) { Rn[j * 17 + j] = h.beta; tau[j] = h.tau; }
+      my_rden = h.rden;
+      if (s == 0) { Rn[j * 17 + j] = h.beta; tau[j] = h.tau; rdenv[j] = h.rden; }
     } else {
-      if (s == 0) Sp[c * 17 + j] = __fmul_rn(gc, h.rden);  // v_c . v_j
+      if (s == 0) Sp[c * 16 + j] = __fmul_rn(__fmul_rn(gc, my_rden), h.rden);  // v_c . v_j
     }
   }
   __syncthreads();
@@ -126,7 +138,8 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
   float* Rn = Rd + 272;
   float* Sp = Rn + 272;
   float* tau = Sp + 272;
-  float* part = tau + 16;  // 128 floats
+  float* rdenv = tau + 16;
+  float* part = rdenv + 16;  // 128 floats
   uint64_t* bar = reinterpret_cast<uint64_t*>(sm + 3968);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + 3976);
   float* Pbuf = reinterpret_cast<float*>(sm + rPbuf);
@@ -207,6 +220,7 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
   for (int tile = 0; tile < ntiles; ++tile) {
     const long long row = t0row + (long long)tile * kT + t;
     const bool valid = row < cend;
+    const uint32_t rowoff = ns::off(t, 0, 128);  // row part of an ns offset; columns add compile-time terms
 #pragma unroll
     for (int c0 = 0; c0 < NP; c0 += 16) {
       float a[16];
@@ -218,8 +232,14 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
       } else {
         tmem_st16(tmem_addr(dA, warp, c0), a);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) tile_store<COR>(AtHi, AtLo, ns::off(t, c0 - 16 + i, 128), a[i]);
+        for (int i = 0; i < 16; ++i) tile_store<COR>(AtHi + rowoff, AtLo + rowoff, ns::coloff(c0 - 16 + i, 128), a[i]);
       }
+    }
+    if (tile + 1 < ntiles) {  // pull the next tile towards L2: one 128-byte line per warp and column
+      const int lane = t & 31;
+      const long long r0 = row - lane + kT;
+      for (int c = lane; c < n; c += 32)
+        if (r0 < cend) prefetch_l2(A + r0 + (long long)c * P.lda);
     }
     if (NP > 16) tmem_wait_st();
 
@@ -234,7 +254,7 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
         }
       }
       __syncthreads();
-      sweep16(Pbuf, Rd, Rn, Sp, tau, part, t);
+      sweep16(Pbuf, Rd, Rn, Sp, tau, rdenv, part, t);
       {
         float rv[16];
         tmem_ld16(tmem_addr(dR, warp, c0), rv);
@@ -244,16 +264,20 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
         }
         tmem_st16(tmem_addr(dR, warp, c0), rv);
       }
-      // reflector block: global V store + both operand layouts
+      // reflector block (scaled here): global V store + both operand layouts
 #pragma unroll
       for (int i4 = 0; i4 < 4; ++i4) {
+        const float4 rd4 = *reinterpret_cast<const float4*>(rdenv + 4 * i4);
         float v[4];
+        v[0] = __fmul_rn(Pbuf[(4 * i4 + 0) * kPS + t], rd4.x);
+        v[1] = __fmul_rn(Pbuf[(4 * i4 + 1) * kPS + t], rd4.y);
+        v[2] = __fmul_rn(Pbuf[(4 * i4 + 2) * kPS + t], rd4.z);
+        v[3] = __fmul_rn(Pbuf[(4 * i4 + 3) * kPS + t], rd4.w);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int i = i4 * 4 + q;
-          v[q] = Pbuf[i * kPS + t];
           if (valid && c0 + i < n) io_store(Q + row + (long long)(c0 + i) * P.ldq, v[q]);
-          if (c0 + 16 < NP) tile_store<COR>(VcHi, VcLo, ns::off(t, i, 128), v[q]);
+          if (c0 + 16 < NP) tile_store<COR>(VcHi + rowoff, VcLo + rowoff, ns::coloff(i, 128), v[q]);
         }
         if (c0 + 16 < NP) rn::store4<COR>(VrHi, VrLo, t, i4, v[0], v[1], v[2], v[3]);
       }
@@ -275,15 +299,18 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
           tmem_ld16(tmem_addr(dG, warp, 0), g);
           tmem_ld16(tmem_addr(dR, warp, c0), rr);
           if (t >= c0 + 16 && t < NP) {
-            float w[16];
+            float acc[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) acc[i] = __fadd_rn(rr[i], g[i]);
+            char* wh = WHi + ns::off(0, t, 16);
+            char* wl = WLo + ns::off(0, t, 16);
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-              float acc = __fadd_rn(rr[i], g[i]);
+              const float w = __fmul_rn(tau[i], acc[i]);
+              rr[i] = __fsub_rn(rr[i], w);
+              tile_store<COR>(wh, wl, (uint32_t)((i >> 2) * ns::kCM + (i & 3) * 4), w);
 #pragma unroll
-              for (int l = 0; l < i; ++l) acc = __fmaf_rn(-Sp[l * 17 + i], w[l], acc);
-              w[i] = __fmul_rn(tau[i], acc);
-              rr[i] = __fsub_rn(rr[i], w[i]);
-              tile_store<COR>(WHi, WLo, ns::off(i, t, 16), w[i]);
+              for (int l = i + 1; l < 16; ++l) acc[l] = __fmaf_rn(-Sp[i * 16 + l], w, acc[l]);
             }
           }
           tmem_st16(tmem_addr(dR, warp, c0), rr);
@@ -311,7 +338,7 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
           float a[16];
           tmem_ld16(tmem_addr(dA, warp, cc), a);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) tile_store<COR>(AtHi, AtLo, ns::off(t, cc - 16 + i, 128), a[i]);
+          for (int i = 0; i < 16; ++i) tile_store<COR>(AtHi + rowoff + ns::coloff(cc - 16, 128), AtLo + rowoff + ns::coloff(cc - 16, 128), ns::coloff(i, 128), a[i]);
         }
       }
     }

@@ -1,5 +1,5 @@
 // Known-answer self test of the tcgen05 primitives in tc05.cuh: every descriptor form the
-// TSQR kernels use (K-major Gram view, MN-major update view, column-group offsets, operand
+// TSQR kernels use (column-wise Gram operands, row-wise update operands, column-group offsets, operand
 // negation, accumulation onto tcgen05.st-initialised TMEM, 1-term and 3-term products) is
 // exercised on caller-provided matrices so that the host can compare against plain fp32/fp64.
 #include "common.cuh"
@@ -13,11 +13,10 @@ constexpr int kRows = 128, kCols = 64;
 constexpr uint32_t kNsTile = tc::ns::bytes(128, 64);  // 36864
 constexpr uint32_t kNsX = tc::ns::bytes(64, 64);      // 18432
 constexpr uint32_t kSmemNs = 4 * kNsTile + 2 * kNsX + 40960 + 1024;
-constexpr uint32_t kSmemRk = 2 * 32768 + 2 * 16384 + 1024;
+constexpr uint32_t kSmemRk = 2 * 32768 + 2 * kNsX + 1024;
 
-// VAR 0: every product on "ns" (no-swizzle, dual-view) buffers -> D1..D4
-// VAR 1: update product with the A operand in the row-wise "rk" buffer (K-major, SWIZZLE_128B)
-//        and B in the swizzled column tile buffer -> D2 only
+// VAR 0: Gram products on column-wise "ns" buffers -> D1, D3
+// VAR 1: update products, A operand in the row-wise "rn" buffer, B in an "ns" buffer -> D2, D4
 template <bool COR, int VAR>
 __global__ void __launch_bounds__(128) selftest_kernel(const float* A, const float* B, const float* X, float* D1,
                                                        float* D2, float* D3, float* D4) {
@@ -44,10 +43,12 @@ __global__ void __launch_bounds__(128) selftest_kernel(const float* A, const flo
     if (t < 64)
       for (int c = 0; c < 64; ++c) tc::tile_store<COR>(Xhi, Xlo, tc::ns::off(t, c, 64), X[t + c * 64]);
   } else {
-    Ahi = base; Alo = Ahi + 32768; Xhi = Alo + 32768; Xlo = Xhi + 16384;
-    for (int c = 0; c < kCols; ++c) tc::tile_store<COR>(Ahi, Alo, tc::rk::off(t, c), A[t + c * kRows]);
+    Ahi = base; Alo = Ahi + 32768; Xhi = Alo + 32768; Xlo = Xhi + kNsX;
+    for (int c4 = 0; c4 < kCols / 4; ++c4)
+      tc::rn::store4<COR>(Ahi, Alo, t, c4, A[t + (4 * c4) * kRows], A[t + (4 * c4 + 1) * kRows], A[t + (4 * c4 + 2) * kRows],
+                          A[t + (4 * c4 + 3) * kRows]);
     if (t < 64)
-      for (int c = 0; c < 64; ++c) tc::tile_store<COR>(Xhi, Xlo, tc::tile_off(t, c, 64), X[t + c * 64]);
+      for (int c = 0; c < 64; ++c) tc::tile_store<COR>(Xhi, Xlo, tc::ns::off(t, c, 64), X[t + c * 64]);
   }
   tc::fence_async_smem();
   tc::fence_before_sync();
@@ -56,7 +57,7 @@ __global__ void __launch_bounds__(128) selftest_kernel(const float* A, const flo
   const uint32_t tm = tmem_base_s;
   const uint32_t dD1 = tm, dD2 = tm + 64, dD3 = tm + 128, dD4 = tm + 160;
 
-  if (VAR == 0) {
+  if (VAR == 1) {
     // D4 starts as B[:, 0:48] (tcgen05.st), then accumulates an update product
     for (int c0 = 0; c0 < 48; c0 += 16) {
       float v[16];
@@ -74,11 +75,10 @@ __global__ void __launch_bounds__(128) selftest_kernel(const float* A, const flo
     if (VAR == 0) {
       const uint32_t bh = tc::smem_u32(Bhi), bl = tc::smem_u32(Blo);
       tc::ns::gram_issue<COR>(dD1, ah, al, 128, 0, bh, bl, 128, 0, 64, 128, false);
-      tc::ns::update_issue<COR>(dD2, ah, al, 0, xh, xl, 64, 0, 0, 64, 64, true, false);
       tc::ns::gram_issue<COR>(dD3, ah, al, 128, 16, bh, bl, 128, 48, 16, 128, false);
-      tc::ns::update_issue<COR>(dD4, ah, al, 16, xh, xl, 64, 16, 16, 48, 16, false, true);
     } else {
-      tc::rk::update_issue<COR>(dD2, ah, al, 0, xh, xl, 64, 0, 0, 64, 64, true, false);
+      tc::rn::update_issue<COR>(dD2, ah, al, 0, xh, xl, 64, 0, 0, 64, 64, true, false);
+      tc::rn::update_issue<COR>(dD4, ah, al, 16, xh, xl, 64, 16, 16, 48, 16, false, true);
     }
     tc::mma_commit(&bar);
   }
@@ -86,19 +86,15 @@ __global__ void __launch_bounds__(128) selftest_kernel(const float* A, const flo
   tc::fence_after_sync();
   float v[16];
   for (int c0 = 0; c0 < 64; c0 += 16) {
-    if (VAR == 0) {
-      tc::tmem_ld16(tc::tmem_addr(dD1, warp, c0), v);
+    tc::tmem_ld16(tc::tmem_addr(VAR == 0 ? dD1 : dD2, warp, c0), v);
 #pragma unroll
-      for (int i = 0; i < 16; ++i) D1[t + (c0 + i) * kRows] = v[i];
-    }
-    tc::tmem_ld16(tc::tmem_addr(dD2, warp, c0), v);
-#pragma unroll
-    for (int i = 0; i < 16; ++i) D2[t + (c0 + i) * kRows] = v[i];
+    for (int i = 0; i < 16; ++i) (VAR == 0 ? D1 : D2)[t + (c0 + i) * kRows] = v[i];
   }
   if (VAR == 0) {
     tc::tmem_ld16(tc::tmem_addr(dD3, warp, 0), v);
 #pragma unroll
     for (int i = 0; i < 16; ++i) D3[t + i * kRows] = v[i];
+  } else {
     for (int c0 = 0; c0 < 48; c0 += 16) {
       tc::tmem_ld16(tc::tmem_addr(dD4, warp, c0), v);
 #pragma unroll
@@ -126,7 +122,7 @@ void launch_selftest(const float* A, const float* B, const float* X, float* D1, 
 // A, B: 128 x 64 col-major (ld 128); X: 64 x 64 col-major (ld 64), all device fp32.
 // D1 = A^T B (rows 0..63 valid) | D2 = -A X | D3[m][n] = sum_r A[r][16+m] B[r][48+n] (m < 48)
 // D4[r][n] = B[r][n] + sum_{j<16} A[r][16+j] X[16+j][16+n] (n < 48); D* are 128-row col-major.
-// variant 0: all four on the no-swizzle dual-view buffers; variant 1: D2 only, row-wise A operand.
+// variant 0 computes D1 and D3 (Gram form), variant 1 computes D2 and D4 (update form).
 extern "C" int tsqr_b200_selftest_mma(int corrected, int variant, const float* A, const float* B, const float* X,
                                       float* D1, float* D2, float* D3, float* D4, void* stream) {
   using namespace tsqr_b200;
