@@ -110,22 +110,21 @@ __device__ __forceinline__ void sweep16(float* Pbuf, const float* Rd, float* Rn,
     const float gc = __fadd_rn(__fadd_rn(gc4.x, gc4.y), __fadd_rn(gc4.z, gc4.w));
     const float gj = __fadd_rn(__fadd_rn(gj4.x, gj4.y), __fadd_rn(gj4.z, gj4.w));
     const HhScal h = hh_scalars(alpha, gj);
-    if (c > j) {
-      const float coef = __fmul_rn(h.tau, __fmaf_rn(gc, h.rden, rjc));
-      const float cv = __fmul_rn(coef, h.rden);
+    // branch-free: lanes with c <= j run the update with a zero coefficient
+    const float coef = __fmul_rn(h.tau, __fmaf_rn(gc, h.rden, rjc));
+    const float cv = (c > j) ? __fmul_rn(coef, h.rden) : 0.f;
 #pragma unroll
-      for (int i = 0; i < 16; ++i) a[i] = __fmaf_rn(-cv, vj[i], a[i]);
-      if (c == j + 1) {
-        float4* dst = reinterpret_cast<float4*>(Pbuf + c * kPS + 16 * s);
+    for (int i = 0; i < 16; ++i) a[i] = __fmaf_rn(-cv, vj[i], a[i]);
+    if (c == j + 1) {
+      float4* dst = reinterpret_cast<float4*>(Pbuf + c * kPS + 16 * s);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) dst[i] = make_float4(a[4 * i], a[4 * i + 1], a[4 * i + 2], a[4 * i + 3]);
-      }
-      if (s == 0) Rn[j * 17 + c] = __fsub_rn(rjc, coef);
-    } else if (c == j) {
-      my_rden = h.rden;
-      if (s == 0) { Rn[j * 17 + j] = h.beta; tau[j] = h.tau; rdenv[j] = h.rden; }
-    } else {
-      if (s == 0) Sp[c * 16 + j] = __fmul_rn(__fmul_rn(gc, my_rden), h.rden);  // v_c . v_j
+      for (int i = 0; i < 4; ++i) dst[i] = make_float4(a[4 * i], a[4 * i + 1], a[4 * i + 2], a[4 * i + 3]);
+    }
+    if (c == j) my_rden = h.rden;
+    if (s == 0) {
+      if (c > j) Rn[j * 17 + c] = __fsub_rn(rjc, coef);
+      else if (c == j) { Rn[j * 17 + j] = h.beta; tau[j] = h.tau; rdenv[j] = h.rden; }
+      else Sp[c * 16 + j] = __fmul_rn(__fmul_rn(gc, my_rden), h.rden);  // v_c . v_j
     }
   }
   __syncthreads();
@@ -264,22 +263,21 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
         }
         tmem_st16(tmem_addr(dR, warp, c0), rv);
       }
-      // reflector block (scaled here): global V store + both operand layouts
+      // reflector block (scaled here): both operand layouts, then the global V store while the
+      // Gram product runs
+      float vout[16];
 #pragma unroll
       for (int i4 = 0; i4 < 4; ++i4) {
         const float4 rd4 = *reinterpret_cast<const float4*>(rdenv + 4 * i4);
-        float v[4];
-        v[0] = __fmul_rn(Pbuf[(4 * i4 + 0) * kPS + t], rd4.x);
-        v[1] = __fmul_rn(Pbuf[(4 * i4 + 1) * kPS + t], rd4.y);
-        v[2] = __fmul_rn(Pbuf[(4 * i4 + 2) * kPS + t], rd4.z);
-        v[3] = __fmul_rn(Pbuf[(4 * i4 + 3) * kPS + t], rd4.w);
+        vout[4 * i4 + 0] = __fmul_rn(Pbuf[(4 * i4 + 0) * kPS + t], rd4.x);
+        vout[4 * i4 + 1] = __fmul_rn(Pbuf[(4 * i4 + 1) * kPS + t], rd4.y);
+        vout[4 * i4 + 2] = __fmul_rn(Pbuf[(4 * i4 + 2) * kPS + t], rd4.z);
+        vout[4 * i4 + 3] = __fmul_rn(Pbuf[(4 * i4 + 3) * kPS + t], rd4.w);
+        if (c0 + 16 < NP) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int i = i4 * 4 + q;
-          if (valid && c0 + i < n) io_store(Q + row + (long long)(c0 + i) * P.ldq, v[q]);
-          if (c0 + 16 < NP) tile_store<COR>(VcHi + rowoff, VcLo + rowoff, ns::coloff(i, 128), v[q]);
+          for (int q = 0; q < 4; ++q) tile_store<COR>(VcHi + rowoff, VcLo + rowoff, ns::coloff(4 * i4 + q, 128), vout[4 * i4 + q]);
+          rn::store4<COR>(VrHi, VrLo, t, i4, vout[4 * i4], vout[4 * i4 + 1], vout[4 * i4 + 2], vout[4 * i4 + 3]);
         }
-        if (c0 + 16 < NP) rn::store4<COR>(VrHi, VrLo, t, i4, v[0], v[1], v[2], v[3]);
       }
       tmem_wait_st();
       if (c0 + 16 < NP) {
@@ -291,6 +289,13 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
           ns::gram_issue<COR>(dG, at_hi_v, at_lo_v, 128, 0, smem_u32(VcHi), smem_u32(VcLo), 128, 0, 16, 128, false);
           mma_commit(bar);
         }
+      }
+      if (valid) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if (c0 + i < n) io_store(Q + row + (long long)(c0 + i) * P.ldq, vout[i]);
+      }
+      if (c0 + 16 < NP) {
         mbar_wait(bar, phase);
         phase ^= 1;
         fence_after_sync();
