@@ -310,8 +310,28 @@ def main():
     if rank == 0:
         peak, peak_src = peaks()
         balg_step = (3.0 * m * n + n * n) * esz            # per GPU
-        balg_build = 2.0 * m * n * esz                      # level-0 build pass: read A, write Q
-        achieved = balg_build / (t_build0 * 1e-3) / 1e9
+        # per-kernel algorithmic bytes: the level-0 reduce pass reads A once
+        # (M*N*s), the level-0 build pass reads the slab again and writes Q (2*M*N*s); the reflector
+        # store/load of the tensor-core path is implementation traffic, not algorithmic bytes.
+        balg_reduce, balg_build = 1.0 * m * n * esz, 2.0 * m * n * esz
+        tc = lib.tsqr_b200_mode_uses_tensor_cores(tq.MODES[args.mode], m) != 0 and n <= 64
+        kname = ("tc_reduce_kernel" if tc else "ts_pass_kernel<REDUCE>", "tc_build_kernel" if tc else "ts_pass_kernel<BUILD>")
+        if t_reduce0 >= t_build0:
+            dom = {"kernel": f"{kname[0]} level 0 (R-reduce pass: read A once" + (", write the reflectors V)" if tc else ")"),
+                   "bytes": balg_reduce, "ms": t_reduce0, "key": "reduce"}
+            others = {"build_level0": t_build0, "upper_levels_total": t_upper}
+        else:
+            dom = {"kernel": f"{kname[1]} level 0 (Q-build pass: read the slab, write Q)", "bytes": balg_build,
+                   "ms": t_build0, "key": "build"}
+            others = {"reduce_level0": t_reduce0, "upper_levels_total": t_upper}
+        achieved = dom["bytes"] / (dom["ms"] * 1e-3) / 1e9
+        traffic = None
+        try:  # dram__bytes_read.sum + dram__bytes_write.sum of that kernel from the committed ncu capture
+            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+                tr = json.load(f)
+            traffic = tr.get(f"{dom['key']}:{args.mode}:m{args.m_log2}:n{n}")
+        except Exception:
+            traffic = None
         line = {
             "metric": "tsqr_gflops", "value": flops(m * P, n) / (ms * 1e-3) / 1e9, "unit": "GFLOP/s",
             "n_gpus": P, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms,
@@ -324,11 +344,10 @@ def main():
                        "l2": f"inputs ({m * n * esz / 2**30:.1f} GiB per GPU) are larger than the 126 MB L2; no flush needed"},
             "hbm_gbs_per_gpu": balg_step / (ms * 1e-3) / 1e9,
             "hbm_frac_step": balg_step / (ms * 1e-3) / 1e9 / peak,
-            "roofline": {"bound": "hbm", "kernel": "ts_pass_kernel<BUILD> level 0 (Q-build pass: read A + checkpoints, write Q)",
-                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                         "peak_source": peak_src, "algorithmic_bytes_per_launch": balg_build,
-                         "ms_per_launch": t_build0,
-                         "other_kernels_ms": {"reduce_level0": t_reduce0, "upper_levels_total": t_upper}},
+            "roofline": {"bound": "hbm", "kernel": dom["kernel"],
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "peak_source": peak_src, "algorithmic_bytes_per_launch": dom["bytes"],
+                         "ms_per_launch": dom["ms"], "other_kernels_ms": others},
             "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e,
             "orthogonality_probe": orth_probe,
         }

@@ -32,6 +32,10 @@ const char* tsqr_b200_last_error(void);
 /* bytes per matrix element for `mode` (2 or 4); 0 if mode is invalid */
 size_t tsqr_b200_io_bytes(int mode);
 
+/* 1 when a TSQR of m rows in `mode` runs on the tcgen05 tensor-core passes (the *_tc_* modes of
+ * reference src/tsqr.hpp:9-20 on tall enough matrices), 0 when it runs on the CUDA-core passes */
+int tsqr_b200_mode_uses_tensor_cores(int mode, size_t m);
+
 /* workspace size in bytes -- replaces mtk::qr::get_working_{q,r,l}_size
  * (reference src/blockqr.cu:34-42) and mtk::qr::buffer::allocate (src/blockqr.hpp:76-95). */
 size_t tsqr_b200_qr_workspace_bytes(size_t m, size_t n, int reorthogonalize);

@@ -27,6 +27,7 @@ SIGNATURES = {
     "tsqr_b200_launch_count": (_c.c_ulonglong, []),
     "tsqr_b200_profile_enable": (None, [_c.c_int]),
     "tsqr_b200_profile_read": (_c.c_int, [_vp, _vp, _c.c_int]),
+    "tsqr_b200_mode_uses_tensor_cores": (_c.c_int, [_c.c_int, _sz]),
     "tsqr_b200_selftest_mma": (_c.c_int, [_c.c_int, _c.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 

@@ -69,6 +69,8 @@ unsigned long long tsqr_b200_launch_count(void) { return g_launches.load(); }
 void tsqr_b200_profile_enable(int on) { profile_enable(on != 0); }
 int tsqr_b200_profile_read(int* labels, float* ms, int cap) { return profile_read(labels, ms, cap); }
 
+int tsqr_b200_mode_uses_tensor_cores(int mode, size_t m) { return mode_valid(mode) && use_tc(mode, (long long)m) ? 1 : 0; }
+
 size_t tsqr_b200_qr_workspace_bytes(size_t m, size_t n, int reorth) {
   if (m == 0 || n == 0 || n > m) return 256;
   return qr_workspace_bytes((long long)m, (long long)n, reorth != 0);

@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
   float* tau = Sp + 272;
   float* rdenv = tau + 16;
   float* part = rdenv + 16;  // 128 floats
+  float* Tp = Rd;            // 16 x 16, written after the sweep is done with Rd
   uint64_t* bar = reinterpret_cast<uint64_t*>(sm + 3968);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + 3976);
   float* Pbuf = reinterpret_cast<float*>(sm + rPbuf);
@@ -296,26 +297,50 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
           if (c0 + i < n) io_store(Q + row + (long long)(c0 + i) * P.ldq, vout[i]);
       }
       if (c0 + 16 < NP) {
+        // while the Gram product runs: T_p = (striu(Sp) + diag(1/tau))^-1, one row per thread
+        // (larft recurrence, a row depends only on its own earlier entries)
+        if (warp == 1 && (t & 31) < 16) {
+          const int i = t & 31;
+          float trow[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            float acc = 0.f;
+#pragma unroll
+            for (int l = 0; l < j; ++l)
+              if (l >= i) acc = __fmaf_rn(trow[l], Sp[l * 16 + j], acc);
+            trow[j] = (j < i) ? 0.f : (j == i ? tau[j] : __fmul_rn(-tau[j], acc));
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j) Tp[i * 16 + j] = trow[j];
+        }
         mbar_wait(bar, phase);
         phase ^= 1;
         fence_after_sync();
+        __syncthreads();
         {  // W = T_p^T (R[J, c] + G[c, :]) for the trailing column c = t; R[J, c] -= W
           float g[16], rr[16];
           tmem_ld16(tmem_addr(dG, warp, 0), g);
           tmem_ld16(tmem_addr(dR, warp, c0), rr);
           if (t >= c0 + 16 && t < NP) {
-            float acc[16];
+            float w[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) acc[i] = __fadd_rn(rr[i], g[i]);
+            for (int i = 0; i < 16; ++i) w[i] = 0.f;
+#pragma unroll
+            for (int l = 0; l < 16; ++l) {
+              const float rhs = __fadd_rn(rr[l], g[l]);
+              const float4* tr = reinterpret_cast<const float4*>(Tp + l * 16);
+              float tl[16];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) { const float4 x = tr[q]; tl[4 * q] = x.x; tl[4 * q + 1] = x.y; tl[4 * q + 2] = x.z; tl[4 * q + 3] = x.w; }
+#pragma unroll
+              for (int i = l; i < 16; ++i) w[i] = __fmaf_rn(tl[i], rhs, w[i]);
+            }
             char* wh = WHi + ns::off(0, t, 16);
             char* wl = WLo + ns::off(0, t, 16);
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-              const float w = __fmul_rn(tau[i], acc[i]);
-              rr[i] = __fsub_rn(rr[i], w);
-              tile_store<COR>(wh, wl, (uint32_t)((i >> 2) * ns::kCM + (i & 3) * 4), w);
-#pragma unroll
-              for (int l = i + 1; l < 16; ++l) acc[l] = __fmaf_rn(-Sp[i * 16 + l], w, acc[l]);
+              rr[i] = __fsub_rn(rr[i], w[i]);
+              tile_store<COR>(wh, wl, (uint32_t)((i >> 2) * ns::kCM + (i & 3) * 4), w[i]);
             }
           }
           tmem_st16(tmem_addr(dR, warp, c0), rr);

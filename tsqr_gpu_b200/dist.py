@@ -10,8 +10,6 @@ BASELINE.json's north_star item (4) asks for.
 import torch
 import torch.distributed as dist
 
-from . import api
-
 
 def stack_r_factors(gathered):
     """gathered: (P, n, n) tensor holding R_p^T row-major (= R_p column-major). Returns the
@@ -21,9 +19,16 @@ def stack_r_factors(gathered):
     return gathered.permute(1, 0, 2).contiguous().view(n, P * n).t()
 
 
-def tsqr_sharded(a_local, mode, ws, group=None, q=None, world_size=None, rank=None):
+def tsqr_sharded(a_local, mode, ws, group=None, q=None, world_size=None, rank=None, ops=None):
     """TSQR of the row-sharded matrix whose local slab is `a_local` (m_p x n, column-major).
-    Returns (q_local, r) with r the full n x n factor (float32, identical on all ranks)."""
+    Returns (q_local, r) with r the full n x n factor (float32, identical on all ranks).
+    `ops` (tests only) replaces the three local steps -- an object with tsqr_reduce / tsqr /
+    tsqr_build of the api module's signatures -- so that the exchange logic can be exercised
+    on CPU tensors over gloo; the default is the CUDA library (no CPU fallback)."""
+    if ops is None:
+        from . import api
+    else:
+        api = ops
     n = a_local.shape[1]
     P = dist.get_world_size(group) if world_size is None else world_size
     p = dist.get_rank(group) if rank is None else rank
@@ -31,8 +36,9 @@ def tsqr_sharded(a_local, mode, ws, group=None, q=None, world_size=None, rank=No
     if P == 1:
         gathered = r_local.t().contiguous().view(1, n, n)
     else:
-        gathered = torch.empty((P, n, n), dtype=torch.float32, device=a_local.device)
-        dist.all_gather_into_tensor(gathered, r_local.t().contiguous(), group=group)
+        flat = torch.empty((P * n, n), dtype=torch.float32, device=a_local.device)   # 2-D: accepted by nccl and gloo
+        dist.all_gather_into_tensor(flat, r_local.t().contiguous(), group=group)
+        gathered = flat.view(P, n, n)
     stacked = stack_r_factors(gathered)
     q_root, r = api.tsqr(stacked, "fp32_notc")                       # redundant root QR
     b = q_root[p * n:(p + 1) * n]                                    # column-major view, ld = P*n
