@@ -1,6 +1,7 @@
 #include "driver.h"
 #include "common.cuh"
 #include <algorithm>
+#include <cstdlib>
 #include <mutex>
 
 namespace tsqr_b200 {
@@ -71,7 +72,7 @@ static Plan make_plan_tc(long long m, int n, int max_chunks0) {
     if (rows <= NP + 8LL * H) {
       tiles_pc = (rows > NP) ? (rows - NP + H - 1) / H : 0;
     } else if (level == 0) {
-      const long long want = max_chunks0 > 0 ? max_chunks0 : 2LL * device_sm_count();  // 2 CTAs per SM
+      const long long want = max_chunks0 > 0 ? max_chunks0 : (long long)cs_reduce_ctas_per_sm(NP) * device_sm_count();
       const long long per = (rows + want - 1) / want;
       tiles_pc = std::max<long long>(4, (per - NP + H - 1) / H);
     } else {
@@ -191,7 +192,9 @@ const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long ld
       TcParams p = tc_level_params(plan, li, a, lda, q, ldq, ws);
       ProfScope prof(s, (int)li * 2);
       const IoType io = li == 0 ? mode_io(mode) : IoType::f32;
-      launch_tc_reduce(p, mode_is_cor(mode), io, io, s);
+      static const bool use_tc_reduce = [] { const char* e = std::getenv("TSQR_B200_REDUCE"); return e && e[0] == 't'; }();
+      if (use_tc_reduce) launch_tc_reduce(p, mode_is_cor(mode), io, io, s);
+      else launch_cs_reduce(p, io, io, s);
     }
     return ws + plan.levels.back().S_off;
   }
