@@ -68,10 +68,11 @@ def main():
         print(f"{100*s/tot_s:5.1f}% smp {100*e/tot_e:5.1f}% ins  {loc}  {text}")
 
 def kern_sub_matches(ncu_name, mangled_sub):
-    # mangled: tc_reduce_kernelILi64ELb1EffE -> match on base name and template args loosely
-    base = re.search(r"(tc_\w+?_kernel)", mangled_sub).group(1)
-    np_ = re.search(r"ILi(\d+)ELb([01])", mangled_sub)
-    return base in ncu_name and f"(int){np_.group(1)}, (bool){np_.group(2)}" in ncu_name
+    # mangled: tc_reduce_kernelILi64ELb1EffE / cs_reduce_kernelILi64ELi4EffE -> base name + first two template args
+    base = re.search(r"([a-z]+_[a-z]+_kernel)", mangled_sub).group(1)
+    m = re.search(r"ILi(\d+)EL([bi])(\d+)", mangled_sub)
+    second = f"(bool){m.group(3)}" if m.group(2) == "b" else f"(int){m.group(3)}"
+    return base in ncu_name and f"(int){m.group(1)}, {second}" in ncu_name
 
 if __name__ == "__main__":
     main()

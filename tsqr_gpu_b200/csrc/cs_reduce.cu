@@ -58,21 +58,27 @@ struct CsSmem {
   static constexpr uint32_t kBytes = oRden + NP * 4 + 16;
 };
 
+// packed fp32 pairs (Blackwell FFMA2): two fused multiply-adds per instruction, same rounding
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+
 // the 16 Householder steps of panel PJ (columns [16 PJ, 16 PJ + 16)) applied to every column
-// >= 16 PJ of the tile. KP = NP / 16 column groups per thread.
+// >= 16 PJ of the tile. KP = NP / 16 column groups per thread; a[k][i] packs rows 2i, 2i+1.
 template <int PJ, int KP>
-__device__ __forceinline__ void sweep_panel(float (&a)[KP][16], float* tileS, float* Rs, float* part, float* rdenv,
+__device__ __forceinline__ void sweep_panel(f32x2 (&a)[KP][8], float* tileS, float* Rs, float* part, float* rdenv,
                                             int LD, int t) {
   const int c16 = t & 15, s = t >> 4, lane = t & 31, warp = t >> 5;
 #pragma unroll 1
   for (int jl = 0; jl < 16; ++jl) {
     const int j = 16 * PJ + jl;
     __syncwarp();  // column j of this row segment was published by a lane of this half warp
-    float vj[16];
+    f32x2 vj[8];
     {
-      const float4* src = reinterpret_cast<const float4*>(tileS + j * kPS + 16 * s);
+      const ulonglong2* src = reinterpret_cast<const ulonglong2*>(tileS + j * kPS + 16 * s);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { const float4 v = src[i]; vj[4 * i] = v.x; vj[4 * i + 1] = v.y; vj[4 * i + 2] = v.z; vj[4 * i + 3] = v.w; }
+      for (int i = 0; i < 4; ++i) { const ulonglong2 v = src[i]; vj[2 * i] = v.x; vj[2 * i + 1] = v.y; }
     }
     // R entries of row j are read before the barrier and rewritten after it
     const float alpha = Rs[j * LD + j];
@@ -82,12 +88,12 @@ __device__ __forceinline__ void sweep_panel(float (&a)[KP][16], float* tileS, fl
     float* pb = part + (jl & 1) * (KP * 64);
 #pragma unroll
     for (int k = PJ; k < KP; ++k) {
-      float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
+      f32x2 q0 = 0ull, q1 = 0ull;
 #pragma unroll
-      for (int i = 0; i < 16; i += 4) {
-        p0 = __fmaf_rn(vj[i], a[k][i], p0); p1 = __fmaf_rn(vj[i + 1], a[k][i + 1], p1);
-        p2 = __fmaf_rn(vj[i + 2], a[k][i + 2], p2); p3 = __fmaf_rn(vj[i + 3], a[k][i + 3], p3);
-      }
+      for (int i = 0; i < 8; i += 2) { q0 = fma2(vj[i], a[k][i], q0); q1 = fma2(vj[i + 1], a[k][i + 1], q1); }
+      float p0, p1, p2, p3;
+      unpack2(q0, p0, p1);
+      unpack2(q1, p2, p3);
       float p = __fadd_rn(__fadd_rn(p0, p1), __fadd_rn(p2, p3));
       p = __fadd_rn(p, __shfl_xor_sync(kFull, p, 16));
       if (lane < 16) pb[(c16 + 16 * k) * 4 + warp] = p;
@@ -102,30 +108,37 @@ __device__ __forceinline__ void sweep_panel(float (&a)[KP][16], float* tileS, fl
       const float g = __fadd_rn(__fadd_rn(g4.x, g4.y), __fadd_rn(g4.z, g4.w));
       const float coef = __fmul_rn(h.tau, __fmaf_rn(g, h.rden, rjc[k]));
       const bool active = (k > PJ) || (c16 > jl);
-      const float cv = active ? __fmul_rn(coef, h.rden) : 0.f;
+      const float ncv = active ? -__fmul_rn(coef, h.rden) : 0.f;
+      const f32x2 ncv2 = pack2(ncv, ncv);
 #pragma unroll
-      for (int i = 0; i < 16; ++i) a[k][i] = __fmaf_rn(-cv, vj[i], a[k][i]);
+      for (int i = 0; i < 8; ++i) a[k][i] = fma2(ncv2, vj[i], a[k][i]);
       if (s == 0 && active) Rs[j * LD + c] = __fsub_rn(rjc[k], coef);
-      if (c == j + 1) {  // publish the next pivot column (raw, unscaled)
-        float4* dst = reinterpret_cast<float4*>(tileS + c * kPS + 16 * s);
+    }
+    if (c16 == jl + 1) {  // publish the next pivot column of this panel (raw, unscaled)
+      ulonglong2* dst = reinterpret_cast<ulonglong2*>(tileS + (j + 1) * kPS + 16 * s);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) dst[i] = make_float4(a[k][4 * i], a[k][4 * i + 1], a[k][4 * i + 2], a[k][4 * i + 3]);
-      }
+      for (int i = 0; i < 4; ++i) dst[i] = make_ulonglong2(a[PJ][2 * i], a[PJ][2 * i + 1]);
     }
     if (s == 0 && c16 == jl) { Rs[j * LD + j] = h.beta; rdenv[j] = h.rden; }
+  }
+  if (PJ + 1 < KP && c16 == 0) {  // first pivot column of the next panel
+    constexpr int KN = PJ + 1 < KP ? PJ + 1 : PJ;
+    ulonglong2* dst = reinterpret_cast<ulonglong2*>(tileS + (16 * (PJ + 1)) * kPS + 16 * s);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i] = make_ulonglong2(a[KN][2 * i], a[KN][2 * i + 1]);
   }
 }
 
 template <int PJ, int KP>
 struct SweepAll {
-  static __device__ __forceinline__ void run(float (&a)[KP][16], float* tileS, float* Rs, float* part, float* rdenv, int LD, int t) {
+  static __device__ __forceinline__ void run(f32x2 (&a)[KP][8], float* tileS, float* Rs, float* part, float* rdenv, int LD, int t) {
     sweep_panel<PJ, KP>(a, tileS, Rs, part, rdenv, LD, t);
     SweepAll<PJ + 1, KP>::run(a, tileS, Rs, part, rdenv, LD, t);
   }
 };
 template <int KP>
 struct SweepAll<KP, KP> {
-  static __device__ __forceinline__ void run(float (&)[KP][16], float*, float*, float*, float*, int, int) {}
+  static __device__ __forceinline__ void run(f32x2 (&)[KP][8], float*, float*, float*, float*, int, int) {}
 };
 
 template <int NP, int MINB, typename TIn, typename TQ>
@@ -207,12 +220,12 @@ __global__ void __launch_bounds__(kT, MINB) cs_reduce_kernel(const TcParams P) {
         if (r0 < cend) tc::prefetch_l2(A + r0 + (long long)c * P.lda);
     }
     __syncthreads();
-    float a[KP][16];
+    f32x2 a[KP][8];
 #pragma unroll
     for (int k = 0; k < KP; ++k) {
-      const float4* src = reinterpret_cast<const float4*>(tileS + (c16 + 16 * k) * kPS + 16 * s);
+      const ulonglong2* src = reinterpret_cast<const ulonglong2*>(tileS + (c16 + 16 * k) * kPS + 16 * s);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { const float4 v = src[i]; a[k][4 * i] = v.x; a[k][4 * i + 1] = v.y; a[k][4 * i + 2] = v.z; a[k][4 * i + 3] = v.w; }
+      for (int i = 0; i < 4; ++i) { const ulonglong2 v = src[i]; a[k][2 * i] = v.x; a[k][2 * i + 1] = v.y; }
     }
     SweepAll<0, KP>::run(a, tileS, Rs, part, rdenv, LD, t);
     __syncthreads();
