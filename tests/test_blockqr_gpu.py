@@ -51,3 +51,29 @@ def test_blockqr_overwrites_a_only_when_wide(cuda, oracle):
     tq.qr(a, "fp32_notc")
     torch.cuda.synchronize()
     assert torch.equal(a, a0)
+
+
+@pytest.mark.parametrize("mode", ["fp32_tc_cor", "tf32_tc_cor"])
+@pytest.mark.parametrize("m,n", [(4096, 128), (5000, 200), (2048, 65), (6000, 320)])
+@pytest.mark.parametrize("reorth", [False, True])
+def test_blockqr_tensor_core_modes(cuda, oracle, mode, m, n, reorth):
+    """n > 64 in a *_tc_cor mode: TSQR panels and both projection GEMMs (tcgen05, hi/lo corrected)."""
+    from helpers import run_qr
+    a = oracle.uniform_matrix(m, n, seed=n + 1)
+    q, r, a_in = run_qr(a, mode, reorth)
+    assert np.isfinite(q).all() and np.isfinite(r).all()
+    orth, res = oracle.orthogonality(q), oracle.residual(q, r, a_in)
+    st, qo, ro = oracle.ref_blockqr(a, reorth)
+    print(f"{mode} {m}x{n} reorth={reorth}: orth {orth:.2e} (ref alg {oracle.orthogonality(qo):.2e}) res {res:.2e}")
+    assert orth <= max(2 * oracle.orthogonality(qo), 3e-6), (orth, oracle.orthogonality(qo))
+    assert res <= max(2 * oracle.residual(qo, ro, a), 3e-6), (res, oracle.residual(qo, ro, a))
+    _, rl = oracle.lapack_qr(a_in, np.float64)
+    assert oracle.r_rel_diff(r, rl) < 3e-5
+
+
+def test_blockqr_tensor_core_nocor(cuda, oracle):
+    from helpers import run_qr
+    a = oracle.uniform_matrix(8192, 192, seed=4)
+    for mode in ("fp32_tc_nocor", "tf32_tc_nocor", "fp16_tc_nocor"):
+        q, r, a_in = run_qr(a, mode, True)
+        assert oracle.orthogonality(q) < 5e-3 and oracle.residual(q, r, a_in) < 5e-3, mode

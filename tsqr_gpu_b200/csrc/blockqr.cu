@@ -164,7 +164,7 @@ QrWs carve(long long m, long long n, bool reorth) {
     if (w.nslabs < 1) w.nslabs = 1;
     w.rows_per_slab = ((m + w.nslabs - 1) / w.nslabs + kSlabRows - 1) / kSlabRows * kSlabRows;
     w.nslabs = (int)((m + w.rows_per_slab - 1) / w.rows_per_slab);
-    w.cp_off = take((size_t)w.nslabs * kbmax * kNB);
+    w.cp_off = take((size_t)2 * w.nslabs * kbmax * kNB);  // the tensor-core product writes two slots per slab
     w.c_off = take((size_t)kbmax * kNB);
     w.s_off = take(reorth ? (size_t)kbmax * kNB : 0);
     w.rcol_off = take((size_t)n * kNB);
@@ -174,9 +174,19 @@ QrWs carve(long long m, long long n, bool reorth) {
   return w;
 }
 
+void reduce_partials_launch(const float* Cp, int nslots, size_t count, float* C, cudaStream_t s) {
+  reduce_partials<<<(unsigned)std::min<size_t>((count + 255) / 256, 1024), 256, 0, s>>>(Cp, nslots, count, C);
+  note_launch();
+}
+
 template <typename T>
-void project(const T* Q1, long long ldq, int kb, T* Y, long long ldy, int nb, long long m, const QrWs& w, float* ws,
+void project(int mode, const T* Q1, long long ldq, int kb, T* Y, long long ldy, int nb, long long m, const QrWs& w, float* ws,
              float* Cout, cudaStream_t s) {
+  if (use_tc(mode, m)) {  // tcgen05 path: both GEMMs on the tensor cores
+    launch_tc_project(mode_is_cor(mode), sizeof(T) == 2 ? IoType::f16 : IoType::f32, Q1, ldq, kb, Y, ldy, nb, m, w.nslabs,
+                      w.rows_per_slab, ws + w.cp_off, Cout, reduce_partials_launch, s);
+    return;
+  }
   dim3 grid(w.nslabs, (kb + 63) / 64);
   gemm_tn_partial<T><<<grid, 256, 0, s>>>(Q1, ldq, kb, Y, ldy, nb, m, w.rows_per_slab, ws + w.cp_off);
   note_launch();
@@ -205,7 +215,7 @@ int qr_typed(int mode, bool reorth, T* q, long long ldq, T* r, long long ldr, T*
     const int kb = (int)c0;
     T* A2 = a + c0 * lda;
     T* Q2 = q + c0 * ldq;
-    if (kb > 0) project<T>(q, ldq, kb, A2, lda, nb, m, w, ws, ws + w.c_off, s);
+    if (kb > 0) project<T>(mode, q, ldq, kb, A2, lda, nb, m, w, ws, ws + w.c_off, s);
     Plan plan = make_plan_for(mode, m, nb);
     const float* r22 = tsqr_reduce(plan, mode, A2, lda, Q2, ldq, tws, s);
     if (kb > 0) copy_block<<<(kb * nb + 255) / 256, 256, 0, s>>>(ws + w.c_off, kb, Rcol, ldrc, kb, nb);
@@ -215,7 +225,7 @@ int qr_typed(int mode, bool reorth, T* q, long long ldq, T* r, long long ldr, T*
     tsqr_build(plan, mode, A2, lda, Q2, ldq, nullptr, 0, tws, s);
     if (reorth && kb > 0) {
       // second projection and second TSQR of the panel (CGS2), then fix up R
-      project<T>(q, ldq, kb, Q2, ldq, nb, m, w, ws, ws + w.s_off, s);
+      project<T>(mode, q, ldq, kb, Q2, ldq, nb, m, w, ws, ws + w.s_off, s);
       const float* wfac = tsqr_reduce(plan, mode, Q2, ldq, Q2, ldq, tws, s);
       float* Wm = ws + w.w_off;
       float* R22old = Wm + kNB * kNB;

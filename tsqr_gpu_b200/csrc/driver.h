@@ -70,6 +70,12 @@ void store_r(const float* r32, int n, void* r, long long ldr, IoType t, cudaStre
 void tsqr_full(int mode, void* q, long long ldq, void* r, long long ldr, const void* a, long long lda,
                long long m, int n, float* ws, size_t ws_bytes, cudaStream_t s);
 
+// Y <- Y - X (X^T Y) on the tensor cores (tc_project.cu); C receives X^T Y (kb x nb, ld kb), Cp holds
+// 2 * nslabs partial products, `reduce` sums partial slots in fixed order.
+void launch_tc_project(bool corrected, IoType io, const void* X, long long ldx, int kb, void* Y, long long ldy, int nb,
+                       long long M, int nslabs, long long rows_per_slab, float* Cp, float* C,
+                       void (*reduce)(const float*, int, size_t, float*, cudaStream_t), cudaStream_t s);
+
 // BlockQR for any n <= m (panels of kMaxN columns); overwrites A when n > kMaxN
 // (reference src/blockqr.cu:45-178, :180-390).
 size_t qr_workspace_bytes(long long m, long long n, bool reorth);
