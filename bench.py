@@ -315,7 +315,7 @@ def main():
         # store/load of the tensor-core path is implementation traffic, not algorithmic bytes.
         balg_reduce, balg_build = 1.0 * m * n * esz, 2.0 * m * n * esz
         tc = lib.tsqr_b200_mode_uses_tensor_cores(tq.MODES[args.mode], m) != 0 and n <= 64
-        kname = ("tc_reduce_kernel" if tc else "ts_pass_kernel<REDUCE>", "tc_build_kernel" if tc else "ts_pass_kernel<BUILD>")
+        kname = ("cs_reduce_kernel" if tc else "ts_pass_kernel<REDUCE>", "tc_build_kernel" if tc else "ts_pass_kernel<BUILD>")
         if t_reduce0 >= t_build0:
             dom = {"kernel": f"{kname[0]} level 0 (R-reduce pass: read A once" + (", write the reflectors V)" if tc else ")"),
                    "bytes": balg_reduce, "ms": t_reduce0, "key": "reduce"}
