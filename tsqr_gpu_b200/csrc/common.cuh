@@ -31,4 +31,10 @@ constexpr unsigned kFullMask = 0xffffffffu;
 // every kernel launch of the library is counted (reported by tsqr_b200_launch_count)
 void note_launch(unsigned n = 1);
 
+// packed fp32 pairs (Blackwell FFMA2): two fused multiply-adds per instruction, same rounding
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+
 }  // namespace tsqr_b200
