@@ -12,11 +12,12 @@ a = torch.empty((n, m), device="cuda").uniform_(-1, 1).t()
 q, r = tq.qr(a, mode)
 q, r = tq.qr(a, mode)
 torch.cuda.synchronize()
-out = (ctypes.c_ulonglong * 9)()
+out = (ctypes.c_ulonglong * 14)()
 lib.tsqr_b200_debug_phases.argtypes = [ctypes.POINTER(ctypes.c_ulonglong)]
 rc = lib.tsqr_b200_debug_phases(out)
-names = ["wait loads + ns staging", "S mma", "raw spill", "combine", "T_p rows", "solve", "rn staging", "Q mma (+next loads issue)", "Q store"]
-tot = sum(out)
+names = ["wait loads + ns staging", "S mma", "raw spill", "combine", "T_p rows", "solve", "rn staging", "Q mma (+next loads issue)", "Q store",
+         "  solve: accumulate", "  solve: ldtm + shuffles", "  solve: T_p apply", "  solve: stores + exchange + sttm", "-"]
+tot = sum(out[:9])
 print("rc", rc, "total cycles", tot)
 for nm, v in zip(names, out):
     print(f"{nm:28s} {v:12d} {100.0 * v / max(tot, 1):5.1f}%")

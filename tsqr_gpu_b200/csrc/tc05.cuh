@@ -36,6 +36,14 @@ __device__ __forceinline__ void tile_store(char* hi, char* lo, uint32_t off, flo
   if (COR) *reinterpret_cast<float*>(lo + off) = __fsub_rn(x, h);
 }
 
+// two values that are adjacent in the tile layout (8-byte aligned offset)
+template <bool COR>
+__device__ __forceinline__ void tile_store2(char* hi, char* lo, uint32_t off, float x0, float x1) {
+  const float h0 = to_tf32_rna(x0), h1 = to_tf32_rna(x1);
+  *reinterpret_cast<float2*>(hi + off) = make_float2(h0, h1);
+  if (COR) *reinterpret_cast<float2*>(lo + off) = make_float2(__fsub_rn(x0, h0), __fsub_rn(x1, h1));
+}
+
 // ---- descriptors
 // shared-memory matrix descriptor, version 1 (Blackwell); layout_type 0 = no swizzle
 __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes,

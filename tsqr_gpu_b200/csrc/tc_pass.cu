@@ -397,13 +397,17 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
 // optional per-phase cycle counters of the build pass (make PHASES=1; tools/phase_clocks.py)
 #ifdef TSQR_B200_PHASES
 __device__ unsigned long long g_phase_clk[16];
-#define PH_INIT() unsigned long long ph_acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long ph_t = clock64()
+#define PH_INIT() unsigned long long ph_acc[14] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long ph_s = 0; unsigned long long ph_t = clock64()
 #define PH(i) do { const unsigned long long ph_now = clock64(); ph_acc[i] += ph_now - ph_t; ph_t = ph_now; } while (0)
-#define PH_FINI() do { if (threadIdx.x == 0 && blockIdx.x == 0) for (int i = 0; i < 9; ++i) g_phase_clk[i] = ph_acc[i]; } while (0)
+#define PHS0() do { ph_s = clock64(); } while (0)
+#define PHS(i) do { const unsigned long long ph_now = clock64(); ph_acc[i] += ph_now - ph_s; ph_s = ph_now; } while (0)
+#define PH_FINI() do { if (threadIdx.x == 0 && blockIdx.x == 0) for (int i = 0; i < 14; ++i) g_phase_clk[i] = ph_acc[i]; } while (0)
 #else
 #define PH_INIT() do {} while (0)
 #define PH(i) do {} while (0)
 #define PH_FINI() do {} while (0)
+#define PHS0() do {} while (0)
+#define PHS(i) do {} while (0)
 #endif
 #include "tc_pass_build.inc"
 
@@ -434,6 +438,6 @@ void launch_tc_build(const TcParams& p, bool corrected, IoType q, cudaStream_t s
 
 #ifdef TSQR_B200_PHASES
 extern "C" int tsqr_b200_debug_phases(unsigned long long* out) {
-  return (int)cudaMemcpyFromSymbol(out, tsqr_b200::g_phase_clk, 9 * sizeof(unsigned long long));
+  return (int)cudaMemcpyFromSymbol(out, tsqr_b200::g_phase_clk, 14 * sizeof(unsigned long long));
 }
 #endif
