@@ -2,11 +2,13 @@
 // tensor-core path (same chunk format as tc_pass.cu: head QR, then [R ; tile] steps; the reflector
 // tails V go to the Q buffer, the chunk's R to the stacked matrix S).
 //
-// Thread t of the 128 owns rows [16s, 16s+16), s = t / 16, of the columns c = t % 16 + 16k
-// (k < NP/16) of a 128 x NP tile, in registers. A Householder step j is
+// Thread t of the 16*RS owns rows [RPT s, RPT s + RPT), s = t / 16, RPT = 128 / RS, of the columns
+// c = t % 16 + 16k (k < NP/16) of a 128 x NP tile, in registers. Two shapes are built: RS = 8
+// (128 threads, 16 rows per thread) and RS = 4 (64 threads, 32 rows per thread: the per-column
+// reduction/scalar work of a step is shared by twice as many FFMA2s). A Householder step j is
 //   * the pivot column's row segment read from shared memory (published by a lane of the same
 //     half warp, so only a __syncwarp orders it),
-//   * per column one 16-term partial dot product per thread, one warp shuffle, a 4-warp combine
+//   * per column one RPT-term partial dot product per thread, one warp shuffle, an RS/2-warp combine
 //     through shared memory (the only block barrier of the step),
 //   * the Householder scalars (rsqrt / rcp), and the rank-1 update of the thread's columns.
 // Measured on B200: this right-looking, unblocked sweep needs fewer instructions per tile than
@@ -23,12 +25,14 @@
 namespace tsqr_b200 {
 namespace {
 
-constexpr int kT = 128;
+constexpr int kTileRows = 128;
 constexpr int kPS = 132;  // tile buffer column stride (floats): 16 B aligned, bank-skewed
 constexpr unsigned kFull = 0xffffffffu;
 
 __device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float rsqrt_approx(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
 
 struct HhScal { float beta, tau, rden; };
 // reflector [1 ; x * rden], R_jj = beta, tau = 1 + |alpha| / norm; zero column: v = 0, tau = 2
@@ -48,98 +52,170 @@ __device__ __forceinline__ HhScal hh_scalars(float alpha, float g) {
   return h;
 }
 
-template <int NP>
+template <int NP, int RS>
 struct CsSmem {
-  static constexpr int LD = NP + 1;
+  static constexpr int LD = NP + 1, NW = RS / 2;
   static constexpr uint32_t oTile = 0;                         // NP x kPS floats
   static constexpr uint32_t oR = oTile + NP * kPS * 4;         // NP x LD floats, R[j * LD + c]
-  static constexpr uint32_t oPart = oR + NP * LD * 4;          // 2 x NP x 4 floats
-  static constexpr uint32_t oRden = oPart + 2 * NP * 4 * 4;    // NP floats
+  static constexpr uint32_t oPart = oR + NP * LD * 4;          // 2 x NP x NW floats
+  static constexpr uint32_t oRden = oPart + 2 * NP * NW * 4;   // NP floats
   static constexpr uint32_t kBytes = oRden + NP * 4 + 16;
 };
 
 
 // the 16 Householder steps of panel PJ (columns [16 PJ, 16 PJ + 16)) applied to every column
 // >= 16 PJ of the tile. KP = NP / 16 column groups per thread; a[k][i] packs rows 2i, 2i+1.
-template <int PJ, int KP>
-__device__ __forceinline__ void sweep_panel(f32x2 (&a)[KP][8], float* tileS, float* Rs, float* part, float* rdenv,
+template <int NW> struct PartVec;
+template <> struct PartVec<4> { static __device__ __forceinline__ float sum(const float* p) {
+  const float4 v = *reinterpret_cast<const float4*>(p); return __fadd_rn(__fadd_rn(v.x, v.y), __fadd_rn(v.z, v.w)); } };
+template <> struct PartVec<2> { static __device__ __forceinline__ float sum(const float* p) {
+  const float2 v = *reinterpret_cast<const float2*>(p); return __fadd_rn(v.x, v.y); } };
+
+template <int PJ, int KP, int RS>
+__device__ __forceinline__ void sweep_panel(f32x2 (&a)[KP][64 / RS], float* tileS, float* Rs, float* part, float* rdenv,
                                             int LD, int t) {
+  constexpr int RPT = kTileRows / RS, NI = RPT / 2, NW = RS / 2;
   const int c16 = t & 15, s = t >> 4, lane = t & 31, warp = t >> 5;
 #pragma unroll 1
   for (int jl = 0; jl < 16; ++jl) {
     const int j = 16 * PJ + jl;
     __syncwarp();  // column j of this row segment was published by a lane of this half warp
-    f32x2 vj[8];
+    f32x2 vj[NI];
     {
-      const ulonglong2* src = reinterpret_cast<const ulonglong2*>(tileS + j * kPS + 16 * s);
+      const ulonglong2* src = reinterpret_cast<const ulonglong2*>(tileS + j * kPS + RPT * s);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { const ulonglong2 v = src[i]; vj[2 * i] = v.x; vj[2 * i + 1] = v.y; }
+      for (int i = 0; i < NI / 2; ++i) { const ulonglong2 v = src[i]; vj[2 * i] = v.x; vj[2 * i + 1] = v.y; }
     }
     // R entries of row j are read before the barrier and rewritten after it
     const float alpha = Rs[j * LD + j];
     float rjc[KP];
 #pragma unroll
     for (int k = PJ; k < KP; ++k) rjc[k] = Rs[j * LD + c16 + 16 * k];
-    float* pb = part + (jl & 1) * (KP * 64);
+    float* pb = part + (jl & 1) * (KP * 16 * NW);
+    {  // dot products: the columns' accumulator chains are interleaved (>= 4 independent FFMA2 chains)
+      constexpr int NA = (KP - PJ) >= 2 ? 2 : 4;  // accumulators per column
+      f32x2 q[KP][NA];
 #pragma unroll
-    for (int k = PJ; k < KP; ++k) {
-      f32x2 q0 = 0ull, q1 = 0ull;
+      for (int k = PJ; k < KP; ++k) {
 #pragma unroll
-      for (int i = 0; i < 8; i += 2) { q0 = fma2(vj[i], a[k][i], q0); q1 = fma2(vj[i + 1], a[k][i + 1], q1); }
-      float p0, p1, p2, p3;
-      unpack2(q0, p0, p1);
-      unpack2(q1, p2, p3);
-      float p = __fadd_rn(__fadd_rn(p0, p1), __fadd_rn(p2, p3));
-      p = __fadd_rn(p, __shfl_xor_sync(kFull, p, 16));
-      if (lane < 16) pb[(c16 + 16 * k) * 4 + warp] = p;
+        for (int u = 0; u < NA; ++u) q[k][u] = 0ull;
+      }
+#pragma unroll
+      for (int i = 0; i < NI; i += NA) {
+#pragma unroll
+        for (int k = PJ; k < KP; ++k) {
+#pragma unroll
+          for (int u = 0; u < NA; ++u) q[k][u] = fma2(vj[i + u], a[k][i + u], q[k][u]);
+        }
+      }
+#pragma unroll
+      for (int k = PJ; k < KP; ++k) {
+        f32x2 qs = add2(q[k][0], q[k][1]);
+        if (NA == 4) qs = add2(qs, add2(q[k][2], q[k][3]));
+        float p0, p1;
+        unpack2(qs, p0, p1);
+        float p = __fadd_rn(p0, p1);
+        p = __fadd_rn(p, __shfl_xor_sync(kFull, p, 16));
+        if (lane < 16) pb[(c16 + 16 * k) * NW + warp] = p;
+      }
     }
     __syncthreads();
-    const float4 gj4 = *reinterpret_cast<const float4*>(pb + j * 4);
-    const HhScal h = hh_scalars(alpha, __fadd_rn(__fadd_rn(gj4.x, gj4.y), __fadd_rn(gj4.z, gj4.w)));
+    const HhScal h = hh_scalars(alpha, PartVec<NW>::sum(pb + j * NW));
 #pragma unroll
     for (int k = PJ; k < KP; ++k) {
       const int c = c16 + 16 * k;
-      const float4 g4 = *reinterpret_cast<const float4*>(pb + c * 4);
-      const float g = __fadd_rn(__fadd_rn(g4.x, g4.y), __fadd_rn(g4.z, g4.w));
+      const float g = PartVec<NW>::sum(pb + c * NW);
       const float coef = __fmul_rn(h.tau, __fmaf_rn(g, h.rden, rjc[k]));
       const bool active = (k > PJ) || (c16 > jl);
       const float ncv = active ? -__fmul_rn(coef, h.rden) : 0.f;
       const f32x2 ncv2 = pack2(ncv, ncv);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) a[k][i] = fma2(ncv2, vj[i], a[k][i]);
+      for (int i = 0; i < NI; ++i) a[k][i] = fma2(ncv2, vj[i], a[k][i]);
       if (s == 0 && active) Rs[j * LD + c] = __fsub_rn(rjc[k], coef);
     }
     if (c16 == jl + 1) {  // publish the next pivot column of this panel (raw, unscaled)
-      ulonglong2* dst = reinterpret_cast<ulonglong2*>(tileS + (j + 1) * kPS + 16 * s);
+      ulonglong2* dst = reinterpret_cast<ulonglong2*>(tileS + (j + 1) * kPS + RPT * s);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) dst[i] = make_ulonglong2(a[PJ][2 * i], a[PJ][2 * i + 1]);
+      for (int i = 0; i < NI / 2; ++i) dst[i] = make_ulonglong2(a[PJ][2 * i], a[PJ][2 * i + 1]);
     }
     if (s == 0 && c16 == jl) { Rs[j * LD + j] = h.beta; rdenv[j] = h.rden; }
   }
   if (PJ + 1 < KP && c16 == 0) {  // first pivot column of the next panel
     constexpr int KN = PJ + 1 < KP ? PJ + 1 : PJ;
-    ulonglong2* dst = reinterpret_cast<ulonglong2*>(tileS + (16 * (PJ + 1)) * kPS + 16 * s);
+    ulonglong2* dst = reinterpret_cast<ulonglong2*>(tileS + (16 * (PJ + 1)) * kPS + RPT * s);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) dst[i] = make_ulonglong2(a[KN][2 * i], a[KN][2 * i + 1]);
+    for (int i = 0; i < NI / 2; ++i) dst[i] = make_ulonglong2(a[KN][2 * i], a[KN][2 * i + 1]);
   }
 }
 
-template <int PJ, int KP>
+template <int PJ, int KP, int RS>
 struct SweepAll {
-  static __device__ __forceinline__ void run(f32x2 (&a)[KP][8], float* tileS, float* Rs, float* part, float* rdenv, int LD, int t) {
-    sweep_panel<PJ, KP>(a, tileS, Rs, part, rdenv, LD, t);
-    SweepAll<PJ + 1, KP>::run(a, tileS, Rs, part, rdenv, LD, t);
+  static __device__ __forceinline__ void run(f32x2 (&a)[KP][64 / RS], float* tileS, float* Rs, float* part, float* rdenv, int LD, int t) {
+    sweep_panel<PJ, KP, RS>(a, tileS, Rs, part, rdenv, LD, t);
+    SweepAll<PJ + 1, KP, RS>::run(a, tileS, Rs, part, rdenv, LD, t);
   }
 };
-template <int KP>
-struct SweepAll<KP, KP> {
-  static __device__ __forceinline__ void run(f32x2 (&)[KP][8], float*, float*, float*, float*, int, int) {}
+template <int KP, int RS>
+struct SweepAll<KP, KP, RS> {
+  static __device__ __forceinline__ void run(f32x2 (&)[KP][64 / RS], float*, float*, float*, float*, int, int) {}
 };
 
-template <int NP, int MINB, typename TIn, typename TQ>
-__global__ void __launch_bounds__(kT, MINB) cs_reduce_kernel(const TcParams P) {
-  using L = CsSmem<NP>;
-  constexpr int LD = L::LD, KP = NP / 16;
+// Step J of the head QR with column c in the registers of thread c (compile-time row indices).
+template <int J, int NP>
+struct HeadSteps {
+  static __device__ __forceinline__ void run(float (&h)[NP], float* pv, int t) {
+    float* pj = pv + (J & 1) * NP;
+    if (t == J) {
+#pragma unroll
+      for (int r = J; r < NP; ++r) pj[r] = h[r];
+    }
+    __syncthreads();
+    constexpr int R0 = J & ~3;
+    // two passes over the shared pivot vector (dots, then update) keep only h[] live in registers
+    float g0 = 0.f, g1 = 0.f, d0 = 0.f, d1 = 0.f, alpha = 0.f;
+#pragma unroll
+    for (int r = R0; r < NP; r += 4) {
+      const float4 v = *reinterpret_cast<const float4*>(pj + r);
+      const float x[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (r + i == J) alpha = x[i];
+        if (r + i > J) {
+          if (i & 1) { g1 = __fmaf_rn(x[i], x[i], g1); d1 = __fmaf_rn(x[i], h[r + i], d1); }
+          else { g0 = __fmaf_rn(x[i], x[i], g0); d0 = __fmaf_rn(x[i], h[r + i], d0); }
+        }
+      }
+    }
+    const HhScal hs = hh_scalars(alpha, __fadd_rn(g0, g1));
+    if (t > J) {
+      const float coef = __fmul_rn(hs.tau, __fmaf_rn(__fadd_rn(d0, d1), hs.rden, h[J]));
+      const float ncv = -__fmul_rn(coef, hs.rden);
+      h[J] = __fsub_rn(h[J], coef);
+#pragma unroll
+      for (int r = R0; r < NP; r += 4) {
+        const float4 v = *reinterpret_cast<const float4*>(pj + r);
+        const float x[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          if (r + i > J) h[r + i] = __fmaf_rn(ncv, x[i], h[r + i]);
+      }
+    } else if (t == J) {
+#pragma unroll
+      for (int r = J + 1; r < NP; ++r) h[r] = __fmul_rn(h[r], hs.rden);
+      h[J] = hs.beta;
+    }
+    HeadSteps<J + 1, NP>::run(h, pv, t);
+  }
+};
+template <int NP>
+struct HeadSteps<NP, NP> {
+  static __device__ __forceinline__ void run(float (&)[NP], float*, int) {}
+};
+
+template <int NP, int RS, int MINB, typename TIn, typename TQ>
+__global__ void __launch_bounds__(16 * RS, MINB) cs_reduce_kernel(const TcParams P) {
+  using L = CsSmem<NP, RS>;
+  constexpr int LD = L::LD, KP = NP / 16, kT = 16 * RS, RPT = kTileRows / RS, NI = RPT / 2, RT = kTileRows / kT;
   extern __shared__ __align__(128) char sm[];
   float* tileS = reinterpret_cast<float*>(sm + L::oTile);
   float* Rs = reinterpret_cast<float*>(sm + L::oR);
@@ -162,25 +238,21 @@ __global__ void __launch_bounds__(kT, MINB) cs_reduce_kernel(const TcParams P) {
       Hs[c * LD + r] = (row < cend && c < n) ? io_load(A + row + (long long)c * P.lda) : 0.f;
     }
     __syncthreads();
-    for (int j = 0; j < NP; ++j) {
-      const float* hj = Hs + j * LD;
-      float g = 0.f;
-      for (int r = j + 1; r < NP; ++r) g = __fmaf_rn(hj[r], hj[r], g);
-      const HhScal h = hh_scalars(hj[j], g);
-      if (t > j && t < NP) {
-        float* hc = Hs + t * LD;
-        float dot = 0.f;
-        for (int r = j + 1; r < NP; ++r) dot = __fmaf_rn(hj[r], hc[r], dot);
-        const float coef = __fmul_rn(h.tau, __fmaf_rn(dot, h.rden, hc[j]));
-        const float cv = __fmul_rn(coef, h.rden);
-        hc[j] = __fsub_rn(hc[j], coef);
-        for (int r = j + 1; r < NP; ++r) hc[r] = __fmaf_rn(-cv, hj[r], hc[r]);
-      }
+    // Column c lives in the registers of thread c (fully unrolled steps, compile-time row indices);
+    // the pivot column goes through a double-buffered shared vector, one barrier per step, and
+    // every thread derives the Householder scalars from it redundantly.
+    {
+      float* pv = part;  // 2 x NP floats (the partial-sum buffers are idle during the head)
+      static_assert(2 * NP <= 2 * NP * (RS / 2), "pivot buffer does not fit");
+      const int cc = t < NP ? t : NP - 1;
+      float h[NP];
+#pragma unroll
+      for (int r = 0; r < NP; ++r) h[r] = Hs[cc * LD + r];
+      HeadSteps<0, NP>::run(h, pv, t);
       __syncthreads();
-      if (t == j) {
-        float* hw = Hs + j * LD;
-        for (int r = j + 1; r < NP; ++r) hw[r] = __fmul_rn(hw[r], h.rden);
-        hw[j] = h.beta;
+      if (t < NP) {
+#pragma unroll
+        for (int r = 0; r < NP; ++r) Hs[t * LD + r] = h[r];
       }
     }
     __syncthreads();
@@ -188,47 +260,64 @@ __global__ void __launch_bounds__(kT, MINB) cs_reduce_kernel(const TcParams P) {
       const int c = idx % NP, j = idx / NP;
       Rs[j * LD + c] = (j <= c) ? Hs[c * LD + j] : 0.f;
     }
-    if (t < NP && cbeg + t < cend) {  // V0 (strictly lower) -> Q head rows
-      for (int j = 0; j < n; ++j) io_store(Q + cbeg + t + (long long)j * P.ldq, t > j ? Hs[j * LD + t] : 0.f);
+    for (int r = t; r < NP; r += kT) {  // V0 (strictly lower) -> Q head rows
+      if (cbeg + r < cend)
+        for (int j = 0; j < n; ++j) io_store(Q + cbeg + r + (long long)j * P.ldq, r > j ? Hs[j * LD + r] : 0.f);
     }
     __syncthreads();
   }
 
   // ---------------- tiles ----------------
   const long long t0row = cbeg + NP;
-  const int ntiles = cend > t0row ? (int)((cend - t0row + kT - 1) / kT) : 0;
+  const int ntiles = cend > t0row ? (int)((cend - t0row + kTileRows - 1) / kTileRows) : 0;
   for (int tile = 0; tile < ntiles; ++tile) {
-    const long long row = t0row + (long long)tile * kT + t;
-    const bool valid = row < cend;
-    {
+    const long long row = t0row + (long long)tile * kTileRows + t;  // this thread: rows row + kT rr
+    {  // a batch of loads in flight per thread before the first shared-memory store
+      constexpr int CB = (32 / RT) < NP ? (32 / RT) : NP;  // 32 loads per thread and batch
       const TIn* ap = A + row;
-#pragma unroll 8
-      for (int c = 0; c < NP; ++c) {
-        tileS[c * kPS + t] = (valid && c < n) ? io_load(ap) : 0.f;
-        ap += P.lda;
+#pragma unroll 1
+      for (int c0 = 0; c0 < NP; c0 += CB) {
+        float v[CB][RT];
+#pragma unroll
+        for (int c = 0; c < CB; ++c) {
+#pragma unroll
+          for (int rr = 0; rr < RT; ++rr)
+            v[c][rr] = (row + kT * rr < cend && c0 + c < n) ? io_load(ap + (long long)c * P.lda + kT * rr) : 0.f;
+        }
+#pragma unroll
+        for (int c = 0; c < CB; ++c) {
+#pragma unroll
+          for (int rr = 0; rr < RT; ++rr) tileS[(c0 + c) * kPS + t + kT * rr] = v[c][rr];
+        }
+        ap += (long long)CB * P.lda;
       }
     }
     if (tile + 1 < ntiles) {  // pull the next tile towards L2: one 128-byte line per warp and column
       const int lane = t & 31;
-      const long long r0 = row - lane + kT;
-      for (int c = lane; c < n; c += 32)
-        if (r0 < cend) tc::prefetch_l2(A + r0 + (long long)c * P.lda);
+#pragma unroll
+      for (int rr = 0; rr < RT; ++rr) {
+        const long long r0 = row - lane + kTileRows + kT * rr;
+        for (int c = lane; c < n; c += 32)
+          if (r0 < cend) tc::prefetch_l2(A + r0 + (long long)c * P.lda);
+      }
     }
     __syncthreads();
-    f32x2 a[KP][8];
+    f32x2 a[KP][NI];
 #pragma unroll
     for (int k = 0; k < KP; ++k) {
-      const ulonglong2* src = reinterpret_cast<const ulonglong2*>(tileS + (c16 + 16 * k) * kPS + 16 * s);
+      const ulonglong2* src = reinterpret_cast<const ulonglong2*>(tileS + (c16 + 16 * k) * kPS + RPT * s);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { const ulonglong2 v = src[i]; a[k][2 * i] = v.x; a[k][2 * i + 1] = v.y; }
+      for (int i = 0; i < NI / 2; ++i) { const ulonglong2 v = src[i]; a[k][2 * i] = v.x; a[k][2 * i + 1] = v.y; }
     }
-    SweepAll<0, KP>::run(a, tileS, Rs, part, rdenv, LD, t);
+    SweepAll<0, KP, RS>::run(a, tileS, Rs, part, rdenv, LD, t);
     __syncthreads();
-    if (valid) {  // V = x_j * rden_j, every column was published (raw) when it became the pivot
+    {  // V = x_j * rden_j, every column was published (raw) when it became the pivot
       TQ* qp = Q + row;
 #pragma unroll 8
       for (int c = 0; c < NP; ++c) {
-        if (c < n) io_store(qp, __fmul_rn(tileS[c * kPS + t], rdenv[c]));
+#pragma unroll
+        for (int rr = 0; rr < RT; ++rr)
+          if (c < n && row + kT * rr < cend) io_store(qp + kT * rr, __fmul_rn(tileS[c * kPS + t + kT * rr], rdenv[c]));
         qp += P.ldq;
       }
     }
@@ -242,32 +331,47 @@ __global__ void __launch_bounds__(kT, MINB) cs_reduce_kernel(const TcParams P) {
   }
 }
 
-template <int NP, typename TIn, typename TQ>
+// row segments per tile: NP = 64 runs the 64-thread shape (RS = 4, 32 rows per thread; measured 8.0 ms
+// vs 8.6 ms at 2^24 x 64), the narrower widths the 128-thread shape. TSQR_B200_CS_RS=4|8 forces one.
+int cs_row_segments(int np) {
+  static const int forced = [] { const char* e = std::getenv("TSQR_B200_CS_RS"); return e ? (e[0] == '8' ? 8 : (e[0] == '4' ? 4 : 0)) : 0; }();
+  return forced ? forced : (np == 64 ? 4 : 8);
+}
+
+template <int NP, int RS, typename TIn, typename TQ>
 void launch_cs_t(const TcParams& p, cudaStream_t s) {
-  constexpr int MINB = NP == 64 ? 4 : 6;
-  auto kern = cs_reduce_kernel<NP, MINB, TIn, TQ>;
-  const int bytes = (int)CsSmem<NP>::kBytes;
+  constexpr int MINB = RS == 8 ? (NP == 64 ? 4 : 6) : (NP == 64 ? 4 : (NP == 32 ? 5 : 8));
+  auto kern = cs_reduce_kernel<NP, RS, MINB, TIn, TQ>;
+  const int bytes = (int)CsSmem<NP, RS>::kBytes;
   TSQR_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-  kern<<<p.nchunks, kT, bytes, s>>>(p);
+  kern<<<p.nchunks, 16 * RS, bytes, s>>>(p);
   note_launch();
   TSQR_CUDA_CHECK(cudaGetLastError());
 }
-template <typename TIn, typename TQ>
+template <int RS, typename TIn, typename TQ>
 void launch_cs_np(const TcParams& p, cudaStream_t s) {
   switch (tc_np(p.n)) {
-    case 16: launch_cs_t<16, TIn, TQ>(p, s); break;
-    case 32: launch_cs_t<32, TIn, TQ>(p, s); break;
-    default: launch_cs_t<64, TIn, TQ>(p, s); break;
+    case 16: launch_cs_t<16, RS, TIn, TQ>(p, s); break;
+    case 32: launch_cs_t<32, RS, TIn, TQ>(p, s); break;
+    default: launch_cs_t<64, RS, TIn, TQ>(p, s); break;
   }
+}
+template <typename TIn, typename TQ>
+void launch_cs_rs(const TcParams& p, cudaStream_t s) {
+  if (cs_row_segments(tc_np(p.n)) == 8) launch_cs_np<8, TIn, TQ>(p, s);
+  else launch_cs_np<4, TIn, TQ>(p, s);
 }
 
 }  // namespace
 
 void launch_cs_reduce(const TcParams& p, IoType in, IoType q, cudaStream_t s) {
   if (in != q) throw std::runtime_error("tsqr_b200: reduce pass needs matching A and Q element types");
-  if (in == IoType::f32) launch_cs_np<float, float>(p, s);
-  else launch_cs_np<__half, __half>(p, s);
+  if (in == IoType::f32) launch_cs_rs<float, float>(p, s);
+  else launch_cs_rs<__half, __half>(p, s);
 }
-int cs_reduce_ctas_per_sm(int np) { return np == 64 ? 4 : 6; }
+int cs_reduce_ctas_per_sm(int np) {
+  if (cs_row_segments(np) == 8) return np == 64 ? 4 : 6;
+  return np == 64 ? 4 : (np == 32 ? 5 : 8);
+}
 
 }  // namespace tsqr_b200
