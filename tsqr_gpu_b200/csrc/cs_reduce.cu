@@ -18,6 +18,8 @@
 // Q = -V X) stays on the tensor cores.
 // Replaces reference src/tcqr32x16.cu:1373-1469 (qr32x16_core with explicit H) and the R-tree
 // levels of src/tsqr.cu:1102-1172.
+#include <cstdlib>
+#include <string>
 #include "common.cuh"
 #include "tc05.cuh"
 #include "ts_pass.h"
@@ -52,9 +54,9 @@ __device__ __forceinline__ HhScal hh_scalars(float alpha, float g) {
   return h;
 }
 
-template <int NP, int RS>
+template <int NP, int RS, int CL>
 struct CsSmem {
-  static constexpr int LD = NP + 1, NW = RS / 2;
+  static constexpr int LD = NP + 1, NW = RS * CL / 32;
   static constexpr uint32_t oTile = 0;                         // NP x kPS floats
   static constexpr uint32_t oR = oTile + NP * kPS * 4;         // NP x LD floats, R[j * LD + c]
   static constexpr uint32_t oPart = oR + NP * LD * 4;          // 2 x NP x NW floats
@@ -71,15 +73,17 @@ template <> struct PartVec<4> { static __device__ __forceinline__ float sum(cons
 template <> struct PartVec<2> { static __device__ __forceinline__ float sum(const float* p) {
   const float2 v = *reinterpret_cast<const float2*>(p); return __fadd_rn(v.x, v.y); } };
 
-template <int PJ, int KP, int RS>
-__device__ __forceinline__ void sweep_panel(f32x2 (&a)[KP][64 / RS], float* tileS, float* Rs, float* part, float* rdenv,
+template <int PJ, int NP, int RS, int CL>
+__device__ __forceinline__ void sweep_panel(f32x2 (&a)[NP / CL][64 / RS], float* tileS, float* Rs, float* part, float* rdenv,
                                             int LD, int t) {
-  constexpr int RPT = kTileRows / RS, NI = RPT / 2, NW = RS / 2;
-  const int c16 = t & 15, s = t >> 4, lane = t & 31, warp = t >> 5;
+  constexpr int KP = NP / CL, RPT = kTileRows / RS, NI = RPT / 2, NW = RS * CL / 32;
+  constexpr int K0 = (16 * PJ) / CL;        // first column group that still has live columns
+  constexpr int JR0 = 16 * PJ - CL * K0;    // lane of this panel's first pivot inside group K0
+  const int cl = t & (CL - 1), s = t / CL, lane = t & 31, warp = t >> 5;
 #pragma unroll 1
   for (int jl = 0; jl < 16; ++jl) {
-    const int j = 16 * PJ + jl;
-    __syncwarp();  // column j of this row segment was published by a lane of this half warp
+    const int j = 16 * PJ + jl, jr = JR0 + jl;
+    __syncwarp();  // column j of this row segment was published by a lane of this warp
     f32x2 vj[NI];
     {
       const ulonglong2* src = reinterpret_cast<const ulonglong2*>(tileS + j * kPS + RPT * s);
@@ -90,74 +94,61 @@ __device__ __forceinline__ void sweep_panel(f32x2 (&a)[KP][64 / RS], float* tile
     const float alpha = Rs[j * LD + j];
     float rjc[KP];
 #pragma unroll
-    for (int k = PJ; k < KP; ++k) rjc[k] = Rs[j * LD + c16 + 16 * k];
-    float* pb = part + (jl & 1) * (KP * 16 * NW);
-    {  // dot products: the columns' accumulator chains are interleaved (>= 4 independent FFMA2 chains)
-      constexpr int NA = (KP - PJ) >= 2 ? 2 : 4;  // accumulators per column
-      f32x2 q[KP][NA];
+    for (int k = K0; k < KP; ++k) rjc[k] = Rs[j * LD + cl + CL * k];
+    float* pb = part + (jl & 1) * (NP * NW);
 #pragma unroll
-      for (int k = PJ; k < KP; ++k) {
+    for (int k = K0; k < KP; ++k) {
+      f32x2 q0 = 0ull, q1 = 0ull;
 #pragma unroll
-        for (int u = 0; u < NA; ++u) q[k][u] = 0ull;
-      }
-#pragma unroll
-      for (int i = 0; i < NI; i += NA) {
-#pragma unroll
-        for (int k = PJ; k < KP; ++k) {
-#pragma unroll
-          for (int u = 0; u < NA; ++u) q[k][u] = fma2(vj[i + u], a[k][i + u], q[k][u]);
-        }
-      }
-#pragma unroll
-      for (int k = PJ; k < KP; ++k) {
-        f32x2 qs = add2(q[k][0], q[k][1]);
-        if (NA == 4) qs = add2(qs, add2(q[k][2], q[k][3]));
-        float p0, p1;
-        unpack2(qs, p0, p1);
-        float p = __fadd_rn(p0, p1);
-        p = __fadd_rn(p, __shfl_xor_sync(kFull, p, 16));
-        if (lane < 16) pb[(c16 + 16 * k) * NW + warp] = p;
-      }
+      for (int i = 0; i < NI; i += 2) { q0 = fma2(vj[i], a[k][i], q0); q1 = fma2(vj[i + 1], a[k][i + 1], q1); }
+      float p0, p1, p2, p3;
+      unpack2(q0, p0, p1);
+      unpack2(q1, p2, p3);
+      float p = __fadd_rn(__fadd_rn(p0, p1), __fadd_rn(p2, p3));
+      if (CL == 16) p = __fadd_rn(p, __shfl_xor_sync(kFull, p, 16));
+      if (CL == 32 || lane < 16) pb[(cl + CL * k) * NW + warp] = p;
     }
     __syncthreads();
     const HhScal h = hh_scalars(alpha, PartVec<NW>::sum(pb + j * NW));
 #pragma unroll
-    for (int k = PJ; k < KP; ++k) {
-      const int c = c16 + 16 * k;
+    for (int k = K0; k < KP; ++k) {
+      const int c = cl + CL * k;
       const float g = PartVec<NW>::sum(pb + c * NW);
       const float coef = __fmul_rn(h.tau, __fmaf_rn(g, h.rden, rjc[k]));
-      const bool active = (k > PJ) || (c16 > jl);
+      const bool active = (k > K0) || (cl > jr);
       const float ncv = active ? -__fmul_rn(coef, h.rden) : 0.f;
       const f32x2 ncv2 = pack2(ncv, ncv);
 #pragma unroll
       for (int i = 0; i < NI; ++i) a[k][i] = fma2(ncv2, vj[i], a[k][i]);
       if (s == 0 && active) Rs[j * LD + c] = __fsub_rn(rjc[k], coef);
     }
-    if (c16 == jl + 1) {  // publish the next pivot column of this panel (raw, unscaled)
+    if (jl < 15 && cl == jr + 1) {  // publish the next pivot column of this panel (raw, unscaled)
       ulonglong2* dst = reinterpret_cast<ulonglong2*>(tileS + (j + 1) * kPS + RPT * s);
 #pragma unroll
-      for (int i = 0; i < NI / 2; ++i) dst[i] = make_ulonglong2(a[PJ][2 * i], a[PJ][2 * i + 1]);
+      for (int i = 0; i < NI / 2; ++i) dst[i] = make_ulonglong2(a[K0][2 * i], a[K0][2 * i + 1]);
     }
-    if (s == 0 && c16 == jl) { Rs[j * LD + j] = h.beta; rdenv[j] = h.rden; }
+    if (s == 0 && cl == jr) { Rs[j * LD + j] = h.beta; rdenv[j] = h.rden; }
   }
-  if (PJ + 1 < KP && c16 == 0) {  // first pivot column of the next panel
-    constexpr int KN = PJ + 1 < KP ? PJ + 1 : PJ;
-    ulonglong2* dst = reinterpret_cast<ulonglong2*>(tileS + (16 * (PJ + 1)) * kPS + RPT * s);
+  if (16 * (PJ + 1) < NP) {  // first pivot column of the next panel
+    constexpr int JN = 16 * (PJ + 1) < NP ? 16 * (PJ + 1) : 0, K1 = JN / CL, L1 = JN % CL;
+    if (cl == L1) {
+      ulonglong2* dst = reinterpret_cast<ulonglong2*>(tileS + JN * kPS + RPT * s);
 #pragma unroll
-    for (int i = 0; i < NI / 2; ++i) dst[i] = make_ulonglong2(a[KN][2 * i], a[KN][2 * i + 1]);
+      for (int i = 0; i < NI / 2; ++i) dst[i] = make_ulonglong2(a[K1][2 * i], a[K1][2 * i + 1]);
+    }
   }
 }
 
-template <int PJ, int KP, int RS>
+template <int PJ, int NP, int RS, int CL>
 struct SweepAll {
-  static __device__ __forceinline__ void run(f32x2 (&a)[KP][64 / RS], float* tileS, float* Rs, float* part, float* rdenv, int LD, int t) {
-    sweep_panel<PJ, KP, RS>(a, tileS, Rs, part, rdenv, LD, t);
-    SweepAll<PJ + 1, KP, RS>::run(a, tileS, Rs, part, rdenv, LD, t);
+  static __device__ __forceinline__ void run(f32x2 (&a)[NP / CL][64 / RS], float* tileS, float* Rs, float* part, float* rdenv, int LD, int t) {
+    sweep_panel<PJ, NP, RS, CL>(a, tileS, Rs, part, rdenv, LD, t);
+    SweepAll<PJ + 1, NP, RS, CL>::run(a, tileS, Rs, part, rdenv, LD, t);
   }
 };
-template <int KP, int RS>
-struct SweepAll<KP, KP, RS> {
-  static __device__ __forceinline__ void run(f32x2 (&)[KP][64 / RS], float*, float*, float*, float*, int, int) {}
+template <int NP, int RS, int CL>
+struct SweepAll<NP / 16, NP, RS, CL> {
+  static __device__ __forceinline__ void run(f32x2 (&)[NP / CL][64 / RS], float*, float*, float*, float*, int, int) {}
 };
 
 // Step J of the head QR with column c in the registers of thread c (compile-time row indices).
@@ -212,16 +203,16 @@ struct HeadSteps<NP, NP> {
   static __device__ __forceinline__ void run(float (&)[NP], float*, int) {}
 };
 
-template <int NP, int RS, int MINB, typename TIn, typename TQ>
-__global__ void __launch_bounds__(16 * RS, MINB) cs_reduce_kernel(const TcParams P) {
-  using L = CsSmem<NP, RS>;
-  constexpr int LD = L::LD, KP = NP / 16, kT = 16 * RS, RPT = kTileRows / RS, NI = RPT / 2, RT = kTileRows / kT;
+template <int NP, int RS, int CL, int MINB, typename TIn, typename TQ>
+__global__ void __launch_bounds__(CL * RS, MINB) cs_reduce_kernel(const TcParams P) {
+  using L = CsSmem<NP, RS, CL>;
+  constexpr int LD = L::LD, KP = NP / CL, kT = CL * RS, RPT = kTileRows / RS, NI = RPT / 2, RT = kTileRows / kT;
   extern __shared__ __align__(128) char sm[];
   float* tileS = reinterpret_cast<float*>(sm + L::oTile);
   float* Rs = reinterpret_cast<float*>(sm + L::oR);
   float* part = reinterpret_cast<float*>(sm + L::oPart);
   float* rdenv = reinterpret_cast<float*>(sm + L::oRden);
-  const int t = threadIdx.x, c16 = t & 15, s = t >> 4;
+  const int t = threadIdx.x, cl = t & (CL - 1), s = t / CL;
   const int n = P.n;
   const TIn* A = reinterpret_cast<const TIn*>(P.A);
   TQ* Q = reinterpret_cast<TQ*>(P.Q);
@@ -243,7 +234,7 @@ __global__ void __launch_bounds__(16 * RS, MINB) cs_reduce_kernel(const TcParams
     // every thread derives the Householder scalars from it redundantly.
     {
       float* pv = part;  // 2 x NP floats (the partial-sum buffers are idle during the head)
-      static_assert(2 * NP <= 2 * NP * (RS / 2), "pivot buffer does not fit");
+      static_assert(L::NW >= 1, "pivot buffer does not fit");
       const int cc = t < NP ? t : NP - 1;
       float h[NP];
 #pragma unroll
@@ -305,11 +296,11 @@ __global__ void __launch_bounds__(16 * RS, MINB) cs_reduce_kernel(const TcParams
     f32x2 a[KP][NI];
 #pragma unroll
     for (int k = 0; k < KP; ++k) {
-      const ulonglong2* src = reinterpret_cast<const ulonglong2*>(tileS + (c16 + 16 * k) * kPS + RPT * s);
+      const ulonglong2* src = reinterpret_cast<const ulonglong2*>(tileS + (cl + CL * k) * kPS + RPT * s);
 #pragma unroll
       for (int i = 0; i < NI / 2; ++i) { const ulonglong2 v = src[i]; a[k][2 * i] = v.x; a[k][2 * i + 1] = v.y; }
     }
-    SweepAll<0, KP, RS>::run(a, tileS, Rs, part, rdenv, LD, t);
+    SweepAll<0, NP, RS, CL>::run(a, tileS, Rs, part, rdenv, LD, t);
     __syncthreads();
     {  // V = x_j * rden_j, every column was published (raw) when it became the pivot
       TQ* qp = Q + row;
@@ -331,47 +322,58 @@ __global__ void __launch_bounds__(16 * RS, MINB) cs_reduce_kernel(const TcParams
   }
 }
 
-// row segments per tile: NP = 64 runs the 64-thread shape (RS = 4, 32 rows per thread; measured 8.0 ms
-// vs 8.6 ms at 2^24 x 64), the narrower widths the 128-thread shape. TSQR_B200_CS_RS=4|8 forces one.
-int cs_row_segments(int np) {
-  static const int forced = [] { const char* e = std::getenv("TSQR_B200_CS_RS"); return e ? (e[0] == '8' ? 8 : (e[0] == '4' ? 4 : 0)) : 0; }();
-  return forced ? forced : (np == 64 ? 4 : 8);
+// Tile shapes (RS row segments x CL column lanes): NP = 64 runs 4 x 16 (64 threads, 32 rows per thread), the
+// narrower widths 8 x 16 (128 threads). Measured at 2^24 x 64 on B200: 4x16 7.7 ms, 8x16 8.9 ms, 4x32 (128
+// threads, a warp = one 32-row segment, lane = column, no shuffle, 16 warps per SM at 128 registers) 10.1 ms.
+// TSQR_B200_CS_SHAPE=8x16 | 4x16 | 4x32 forces one (4x32 needs NP = 64).
+int cs_shape(int np) {
+  static const int forced = [] {
+    const char* e = std::getenv("TSQR_B200_CS_SHAPE");
+    if (!e) return 0;
+    const std::string v(e);
+    return v == "8x16" ? 816 : (v == "4x16" ? 416 : (v == "4x32" ? 432 : 0));
+  }();
+  if (forced == 432 && np != 64) return 816;
+  return forced ? forced : (np == 64 ? 416 : 816);
 }
 
-template <int NP, int RS, typename TIn, typename TQ>
+template <int NP, int RS, int CL, int MINB, typename TIn, typename TQ>
 void launch_cs_t(const TcParams& p, cudaStream_t s) {
-  constexpr int MINB = RS == 8 ? (NP == 64 ? 4 : 6) : (NP == 64 ? 4 : (NP == 32 ? 5 : 8));
-  auto kern = cs_reduce_kernel<NP, RS, MINB, TIn, TQ>;
-  const int bytes = (int)CsSmem<NP, RS>::kBytes;
+  auto kern = cs_reduce_kernel<NP, RS, CL, MINB, TIn, TQ>;
+  const int bytes = (int)CsSmem<NP, RS, CL>::kBytes;
   TSQR_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-  kern<<<p.nchunks, 16 * RS, bytes, s>>>(p);
+  kern<<<p.nchunks, CL * RS, bytes, s>>>(p);
   note_launch();
   TSQR_CUDA_CHECK(cudaGetLastError());
 }
-template <int RS, typename TIn, typename TQ>
-void launch_cs_np(const TcParams& p, cudaStream_t s) {
-  switch (tc_np(p.n)) {
-    case 16: launch_cs_t<16, RS, TIn, TQ>(p, s); break;
-    case 32: launch_cs_t<32, RS, TIn, TQ>(p, s); break;
-    default: launch_cs_t<64, RS, TIn, TQ>(p, s); break;
-  }
-}
 template <typename TIn, typename TQ>
-void launch_cs_rs(const TcParams& p, cudaStream_t s) {
-  if (cs_row_segments(tc_np(p.n)) == 8) launch_cs_np<8, TIn, TQ>(p, s);
-  else launch_cs_np<4, TIn, TQ>(p, s);
+void launch_cs_shape(const TcParams& p, cudaStream_t s) {
+  const int np = tc_np(p.n), shape = cs_shape(np);
+  if (np == 64) {
+    if (shape == 432) launch_cs_t<64, 4, 32, 4, TIn, TQ>(p, s);
+    else if (shape == 416) launch_cs_t<64, 4, 16, 4, TIn, TQ>(p, s);
+    else launch_cs_t<64, 8, 16, 4, TIn, TQ>(p, s);
+  } else if (np == 32) {
+    if (shape == 416) launch_cs_t<32, 4, 16, 5, TIn, TQ>(p, s);
+    else launch_cs_t<32, 8, 16, 6, TIn, TQ>(p, s);
+  } else {
+    if (shape == 416) launch_cs_t<16, 4, 16, 8, TIn, TQ>(p, s);
+    else launch_cs_t<16, 8, 16, 6, TIn, TQ>(p, s);
+  }
 }
 
 }  // namespace
 
 void launch_cs_reduce(const TcParams& p, IoType in, IoType q, cudaStream_t s) {
   if (in != q) throw std::runtime_error("tsqr_b200: reduce pass needs matching A and Q element types");
-  if (in == IoType::f32) launch_cs_rs<float, float>(p, s);
-  else launch_cs_rs<__half, __half>(p, s);
+  if (in == IoType::f32) launch_cs_shape<float, float>(p, s);
+  else launch_cs_shape<__half, __half>(p, s);
 }
 int cs_reduce_ctas_per_sm(int np) {
-  if (cs_row_segments(np) == 8) return np == 64 ? 4 : 6;
-  return np == 64 ? 4 : (np == 32 ? 5 : 8);
+  const int shape = cs_shape(np);
+  if (np == 64) return 4;
+  if (np == 32) return shape == 416 ? 5 : 6;
+  return shape == 416 ? 8 : 6;
 }
 
 }  // namespace tsqr_b200
