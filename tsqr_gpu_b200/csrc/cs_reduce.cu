@@ -36,6 +36,18 @@ __device__ __forceinline__ float rsqrt_approx(float x) { float y; asm("rsqrt.app
 
 __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
 
+// raw element loads: the conversion of fp16 input is kept apart from the load so that a whole batch of
+// loads is in flight before the first use (with __half2float(__ldg(p)) the compiler reuses one register
+// for load + convert and serialises the batch)
+__device__ __forceinline__ float raw_load(const float* p) { return __ldg(p); }
+__device__ __forceinline__ unsigned short raw_load(const __half* p) {
+  unsigned short v; asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(v) : "l"(p)); return v;
+}
+__device__ __forceinline__ float raw_cvt(float v) { return v; }
+__device__ __forceinline__ float raw_cvt(unsigned short v) { return __half2float(__ushort_as_half(v)); }
+template <typename T> struct RawOf { typedef float type; };
+template <> struct RawOf<__half> { typedef unsigned short type; };
+
 struct HhScal { float beta, tau, rden; };
 // reflector [1 ; x * rden], R_jj = beta, tau = 1 + |alpha| / norm; zero column: v = 0, tau = 2
 __device__ __forceinline__ HhScal hh_scalars(float alpha, float g) {
@@ -261,30 +273,52 @@ __global__ void __launch_bounds__(CL * RS, MINB) cs_reduce_kernel(const TcParams
   // ---------------- tiles ----------------
   const long long t0row = cbeg + NP;
   const int ntiles = cend > t0row ? (int)((cend - t0row + kTileRows - 1) / kTileRows) : 0;
-  for (int tile = 0; tile < ntiles; ++tile) {
-    const long long row = t0row + (long long)tile * kTileRows + t;  // this thread: rows row + kT rr
-    {  // a batch of loads in flight per thread before the first shared-memory store
-      constexpr int CB = (32 / RT) < NP ? (32 / RT) : NP;  // 32 loads per thread and batch
-      const TIn* ap = A + row;
+  // Tile i+1 is loaded while tile i's reflectors are stored: a thread overwrites exactly the shared-memory
+  // words it has just read for the V store, so the two are fused column batch by column batch (the loads are
+  // in flight behind the batch's stores) with no barrier in between. STORE = false is the prologue (tile 0).
+  constexpr int CB = (NP < 64 && RT == 1) ? 8 : 16;  // columns per batch (8 where the register cap is 85)
+  auto store_load = [&](int tile_st, int tile_ld) {
+    const long long row_st = t0row + (long long)tile_st * kTileRows + t;  // this thread: rows row + kT rr
+    const long long row_ld = t0row + (long long)tile_ld * kTileRows + t;
+    const bool do_st = tile_st >= 0, do_ld = tile_ld < ntiles;
 #pragma unroll 1
-      for (int c0 = 0; c0 < NP; c0 += CB) {
-        float v[CB][RT];
+    for (int c0 = 0; c0 < NP; c0 += CB) {
+      typename RawOf<TIn>::type v[CB][RT];
+      if (do_ld) {
+        const TIn* ap = A + row_ld + (long long)c0 * P.lda;
+#pragma unroll
+        for (int c = 0; c < CB; ++c) {
+#pragma unroll
+          for (int rr = 0; rr < RT; ++rr) {
+            v[c][rr] = 0;
+            if (row_ld + kT * rr < cend && c0 + c < n) v[c][rr] = raw_load(ap + (long long)c * P.lda + kT * rr);
+          }
+        }
+      }
+      if (do_st) {  // V = x_j * rden_j, every column was published (raw) when it became the pivot
+        TQ* qp = Q + row_st + (long long)c0 * P.ldq;
 #pragma unroll
         for (int c = 0; c < CB; ++c) {
 #pragma unroll
           for (int rr = 0; rr < RT; ++rr)
-            v[c][rr] = (row + kT * rr < cend && c0 + c < n) ? io_load(ap + (long long)c * P.lda + kT * rr) : 0.f;
+            if (c0 + c < n && row_st + kT * rr < cend)
+              io_store(qp + (long long)c * P.ldq + kT * rr, __fmul_rn(tileS[(c0 + c) * kPS + t + kT * rr], rdenv[c0 + c]));
         }
+      }
+      if (do_ld) {
 #pragma unroll
         for (int c = 0; c < CB; ++c) {
 #pragma unroll
-          for (int rr = 0; rr < RT; ++rr) tileS[(c0 + c) * kPS + t + kT * rr] = v[c][rr];
+          for (int rr = 0; rr < RT; ++rr) tileS[(c0 + c) * kPS + t + kT * rr] = raw_cvt(v[c][rr]);
         }
-        ap += (long long)CB * P.lda;
       }
     }
+  };
+  if (ntiles > 0) store_load(-1, 0);
+  for (int tile = 0; tile < ntiles; ++tile) {
     if (tile + 1 < ntiles) {  // pull the next tile towards L2: one 128-byte line per warp and column
       const int lane = t & 31;
+      const long long row = t0row + (long long)tile * kTileRows + t;
 #pragma unroll
       for (int rr = 0; rr < RT; ++rr) {
         const long long r0 = row - lane + kTileRows + kT * rr;
@@ -302,18 +336,9 @@ __global__ void __launch_bounds__(CL * RS, MINB) cs_reduce_kernel(const TcParams
     }
     SweepAll<0, NP, RS, CL>::run(a, tileS, Rs, part, rdenv, LD, t);
     __syncthreads();
-    {  // V = x_j * rden_j, every column was published (raw) when it became the pivot
-      TQ* qp = Q + row;
-#pragma unroll 8
-      for (int c = 0; c < NP; ++c) {
-#pragma unroll
-        for (int rr = 0; rr < RT; ++rr)
-          if (c < n && row + kT * rr < cend) io_store(qp + kT * rr, __fmul_rn(tileS[c * kPS + t + kT * rr], rdenv[c]));
-        qp += P.ldq;
-      }
-    }
-    __syncthreads();
+    store_load(tile, tile + 1);
   }
+  __syncthreads();
 
   // ---------------- chunk result: R -> stacked S ----------------
   for (int idx = t; idx < n * n; idx += kT) {
