@@ -283,7 +283,15 @@ def main():
         a_host.copy_(a.t() if a_pristine is None else a_pristine.t())
         torch.cuda.synchronize()
 
+        # single GPU, n <= 64: the public host-buffer call overlaps the slab transfers with the two passes
+        pipe = tq.HostPipeline(m, n, args.mode, nslabs=8) if (P == 1 and n <= 64 and not args.reorth) else None
+        if pipe is not None:
+            r_host = torch.empty((n, n), dtype=torch.float32, pin_memory=True)
+
         def e2e_step():
+            if pipe is not None:
+                pipe.run(a_host, q_host, r_host)
+                return
             a.t().copy_(a_host, non_blocking=True)
             if P > 1:
                 _, rr = tsqr_sharded(a, args.mode, buf.ws, q=q, world_size=P, rank=rank)
@@ -308,7 +316,9 @@ def main():
         ems /= e2e_steps
         e2e = {"value": flops(m * P, n) / (ems * 1e-3) / 1e9, "unit": "GFLOP/s", "ms_per_step": ems,
                "steps": e2e_steps, "h2d_bytes_per_step": m * n * esz * P,
-               "d2h_bytes_per_step": (m * n * esz + n * n * 4) * P}
+               "d2h_bytes_per_step": (m * n * esz + n * n * 4) * P,
+               "api": ("tsqr_gpu_b200.HostPipeline.run: 8 row slabs, H2D | reduce and build | D2H overlapped on copy streams"
+                       if pipe is not None else "H2D, tsqr_gpu_b200.qr / dist.tsqr_sharded, D2H on one stream")}
 
     if rank == 0:
         peak, peak_src = peaks()

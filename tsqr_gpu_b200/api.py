@@ -5,6 +5,8 @@ Matrices are torch CUDA tensors in column-major layout: shape (m, n), stride (1,
 `to_colmajor` / `colmajor_empty` make such tensors. Everything runs on the current torch
 CUDA stream and never synchronises the host.
 """
+import ctypes
+
 import torch
 
 from ._lib import lib
@@ -207,6 +209,94 @@ def qr_host(a_host, q_host, r_host, a_dev, q_dev, r_dev, mode, reorthogonalize, 
     qr(a_dev, mode, reorthogonalize, buffer, q_dev, r_dev)
     q_host.copy_(q_dev.t(), non_blocking=True)
     r_host.copy_(r_dev.t(), non_blocking=True)
+
+
+_cudart = None
+
+
+def _memcpy2d_async(dst, src, stream):
+    """Strided 2-D copy between a pinned host tensor and a device tensor (both (rows, cols) with unit
+    column stride) as ONE cudaMemcpy2DAsync on `stream`: torch's copy_ would stage a non-contiguous
+    host slice through pageable memory."""
+    global _cudart
+    if _cudart is None:
+        _cudart = ctypes.CDLL("libcudart.so.12")
+        _cudart.cudaMemcpy2DAsync.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t,
+                                              ctypes.c_size_t, ctypes.c_size_t, ctypes.c_int, ctypes.c_void_p]
+        _cudart.cudaMemcpy2DAsync.restype = ctypes.c_int
+    if dst.shape != src.shape or dst.dtype != src.dtype or dst.stride(1) != 1 or src.stride(1) != 1:
+        raise ValueError("memcpy2d: need equal shapes/dtypes and unit inner strides")
+    esz = dst.element_size()
+    rows, cols = dst.shape
+    kind = 4  # cudaMemcpyDefault
+    err = _cudart.cudaMemcpy2DAsync(dst.data_ptr(), dst.stride(0) * esz, src.data_ptr(), src.stride(0) * esz,
+                                    cols * esz, rows, kind, stream.cuda_stream)
+    if err != 0:
+        raise RuntimeError(f"cudaMemcpy2DAsync failed with error {err}")
+
+
+class HostPipeline:
+    """TSQR (n <= 64) of a matrix that lives in pinned HOST memory, overlapped with its own transfers.
+
+    The rows are cut into `nslabs` slabs. Slab s is copied to the device on a copy stream and reduced
+    (tsqr_reduce) as soon as it has arrived; the slab R factors are stacked and factored once (the same
+    root step as the row-sharded multi-GPU path, tsqr_gpu_b200/dist.py); then every slab is built
+    (tsqr_build with its block of the root Q) and copied back while the next slab is being built.
+    The result is the QR factorisation of the whole matrix (R n x n float32).
+    Host matrices are column-major, given as (n, m) row-major pinned tensors."""
+
+    def __init__(self, m, n, mode, nslabs=8, device="cuda"):
+        self.m, self.n, self.mode = m, n, mode
+        md = _mode(mode)
+        self.dtype = io_dtype(md)
+        if n > 64 or n > m:
+            raise InvalidMatrixSize("HostPipeline takes 0 < n <= 64, n <= m")
+        ms = -(-m // nslabs)
+        ms = max(1024, -(-ms // 128) * 128)      # slab height: a multiple of the tile height
+        self.bounds = [(lo, min(m, lo + ms)) for lo in range(0, m, ms)]
+        if len(self.bounds) > 1 and self.bounds[-1][1] - self.bounds[-1][0] < max(n, 1024):
+            lo, _ = self.bounds[-2]              # fold a short tail into the previous slab
+            self.bounds[-2:] = [(lo, m)]
+        self.a = colmajor_empty(m, n, self.dtype, device)
+        self.q = colmajor_empty(m, n, self.dtype, device)
+        self.ws = [torch.empty(lib.tsqr_b200_tsqr_workspace_bytes(hi - lo, n), dtype=torch.uint8, device=device)
+                   for lo, hi in self.bounds]
+        self.h2d, self.d2h = torch.cuda.Stream(device), torch.cuda.Stream(device)
+        S = len(self.bounds)
+        self.ev_in = [torch.cuda.Event() for _ in range(S)]
+        self.ev_out = [torch.cuda.Event() for _ in range(S)]
+        self.ev_start, self.ev_done = torch.cuda.Event(), torch.cuda.Event()
+
+    def run(self, a_host, q_host, r_host):
+        """a_host, q_host: (n, m) pinned; r_host: (n, n) float32 pinned (receives R column-major).
+        Asynchronous: everything is ordered after the current stream's work and the current stream
+        waits for the last copy; synchronise it before reading the host buffers."""
+        from .dist import stack_r_factors
+        n, cur = self.n, torch.cuda.current_stream()
+        self.ev_start.record(cur)
+        self.h2d.wait_event(self.ev_start)
+        self.d2h.wait_event(self.ev_start)
+        with torch.cuda.stream(self.h2d):
+            for s, (lo, hi) in enumerate(self.bounds):
+                _memcpy2d_async(self.a[lo:hi].t(), a_host[:, lo:hi], self.h2d)
+                self.ev_in[s].record(self.h2d)
+        rs = []
+        for s, (lo, hi) in enumerate(self.bounds):
+            cur.wait_event(self.ev_in[s])
+            r_s, _ = tsqr_reduce(self.a[lo:hi], self.mode, self.ws[s], q=self.q[lo:hi])
+            rs.append(r_s.t())                                   # R_s^T row-major = R_s column-major storage
+        stacked = stack_r_factors(torch.stack(rs))
+        q_root, r = tsqr(stacked, "fp32_notc")
+        for s, (lo, hi) in enumerate(self.bounds):
+            tsqr_build(self.a[lo:hi], self.mode, self.ws[s], b=q_root[s * n:(s + 1) * n], q=self.q[lo:hi])
+            self.ev_out[s].record(cur)
+            self.d2h.wait_event(self.ev_out[s])
+            _memcpy2d_async(q_host[:, lo:hi], self.q[lo:hi].t(), self.d2h)
+        with torch.cuda.stream(self.d2h):
+            r_host.copy_(r.t(), non_blocking=True)
+            self.ev_done.record(self.d2h)
+        cur.wait_event(self.ev_done)
+        return r
 
 
 def launch_count():
