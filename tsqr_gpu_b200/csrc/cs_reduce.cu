@@ -53,16 +53,17 @@ struct HhScal { float beta, tau, rden; };
 __device__ __forceinline__ HhScal hh_scalars(float alpha, float g) {
   HhScal h;
   const float nx2 = __fmaf_rn(alpha, alpha, g);
-  if (nx2 > 1e-36f) {
-    const float y = rsqrt_approx(nx2);
-    const float n0 = __fmul_rn(nx2, y);
-    const float norm = __fmaf_rn(__fmul_rn(0.5f, y), __fmaf_rn(-n0, n0, nx2), n0);
-    h.beta = -copysignf(norm, alpha);
-    h.rden = rcp_approx(__fsub_rn(alpha, h.beta));
-    h.tau = __fmaf_rn(fabsf(alpha), rcp_approx(norm), 1.f);
-  } else {
-    h.beta = 0.f; h.rden = 0.f; h.tau = 2.f;
-  }
+  const bool ok = nx2 > 1e-36f;              // branch-free: the zero column is a select at the end
+  const float nx2s = ok ? nx2 : 1.f;
+  const float y = rsqrt_approx(nx2s);
+  const float n0 = __fmul_rn(nx2s, y);
+  const float norm = __fmaf_rn(__fmul_rn(0.5f, y), __fmaf_rn(-n0, n0, nx2s), n0);
+  const float beta = -copysignf(norm, alpha);
+  const float rden = rcp_approx(__fsub_rn(alpha, beta));
+  const float tau = __fmaf_rn(fabsf(alpha), rcp_approx(norm), 1.f);
+  h.beta = ok ? beta : 0.f;
+  h.rden = ok ? rden : 0.f;
+  h.tau = ok ? tau : 2.f;
   return h;
 }
 
