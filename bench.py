@@ -38,6 +38,7 @@ def parse():
     ap.add_argument("--reorth", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-sequential", action="store_true", help="e2e as H2D -> qr -> D2H on one stream (no HostPipeline)")
     return ap.parse_args()
 
 
@@ -284,7 +285,7 @@ def main():
         torch.cuda.synchronize()
 
         # single GPU, n <= 64: the public host-buffer call overlaps the slab transfers with the two passes
-        pipe = tq.HostPipeline(m, n, args.mode, nslabs=8) if (P == 1 and n <= 64 and not args.reorth) else None
+        pipe = tq.HostPipeline(m, n, args.mode, nslabs=8) if (P == 1 and n <= 64 and not args.reorth and not args.e2e_sequential) else None
         if pipe is not None:
             r_host = torch.empty((n, n), dtype=torch.float32, pin_memory=True)
 
