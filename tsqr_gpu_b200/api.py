@@ -235,6 +235,18 @@ def _memcpy2d_async(dst, src, stream):
         raise RuntimeError(f"cudaMemcpy2DAsync failed with error {err}")
 
 
+def slab_bounds(m, n, nslabs):
+    """Row ranges [(lo, hi), ...] of the HostPipeline slabs: contiguous, covering [0, m), heights a multiple
+    of the 128-row tile (except the last), at least 1024 rows and at least n rows each."""
+    ms = -(-m // max(1, nslabs))
+    ms = max(1024, n, -(-ms // 128) * 128)
+    bounds = [(lo, min(m, lo + ms)) for lo in range(0, m, ms)]
+    if len(bounds) > 1 and bounds[-1][1] - bounds[-1][0] < max(n, 1024):
+        lo, _ = bounds[-2]                       # fold a short tail into the previous slab
+        bounds[-2:] = [(lo, m)]
+    return bounds
+
+
 class HostPipeline:
     """TSQR (n <= 64) of a matrix that lives in pinned HOST memory, overlapped with its own transfers.
 
@@ -251,12 +263,7 @@ class HostPipeline:
         self.dtype = io_dtype(md)
         if n > 64 or n > m:
             raise InvalidMatrixSize("HostPipeline takes 0 < n <= 64, n <= m")
-        ms = -(-m // nslabs)
-        ms = max(1024, -(-ms // 128) * 128)      # slab height: a multiple of the tile height
-        self.bounds = [(lo, min(m, lo + ms)) for lo in range(0, m, ms)]
-        if len(self.bounds) > 1 and self.bounds[-1][1] - self.bounds[-1][0] < max(n, 1024):
-            lo, _ = self.bounds[-2]              # fold a short tail into the previous slab
-            self.bounds[-2:] = [(lo, m)]
+        self.bounds = slab_bounds(m, n, nslabs)
         self.a = colmajor_empty(m, n, self.dtype, device)
         self.q = colmajor_empty(m, n, self.dtype, device)
         self.ws = [torch.empty(lib.tsqr_b200_tsqr_workspace_bytes(hi - lo, n), dtype=torch.uint8, device=device)
