@@ -40,7 +40,8 @@ def metrics(q, r, a):
 
 
 def main():
-    m = 1 << int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 24
+    pos = [x for x in sys.argv[1:] if not x.startswith('--')]
+    m = 1 << int(pos[0]) if pos else 1 << 24
     n, cond = 64, 1e6
     ref = None
     so = os.path.join(ROOT, "oracle", "_ref", "libref_tcqr.so")
@@ -49,15 +50,21 @@ def main():
         vp, sz = ctypes.c_void_p, ctypes.c_size_t
         ref.ref_gpu_qr.argtypes = [ctypes.c_int, ctypes.c_int, vp, sz, vp, sz, vp, sz, sz, sz, vp]
         ref.ref_gpu_qr.restype = ctypes.c_int
-    a64 = conditioned(m, n, cond, seed=20261105)
-    for mode in ["fp32_tc_cor", "tf32_tc_cor", "fp16_tc_nocor"]:
+    uniform = "--uniform" in sys.argv      # uniform(-1, 1) inputs (reference src/test.cu:97), all ten compute modes
+    if uniform:
+        g = torch.Generator(device="cuda"); g.manual_seed(20261105)
+        a64 = torch.empty((n, m), dtype=torch.float32, device="cuda").uniform_(-1, 1, generator=g).t()
+        cond = None
+    else:
+        a64 = conditioned(m, n, cond, seed=20261105)
+    for mode in (list(tq.MODES) if uniform else ["fp32_tc_cor", "tf32_tc_cor", "fp16_tc_nocor"]):
         dt = tq.io_dtype(mode)
         a0 = tq.to_colmajor(a64.to(dt))
         q = tq.colmajor_empty(m, n, dt); r = torch.zeros((n, n), dtype=dt, device="cuda").t()
         tq.qr(a0, mode, False, None, q, r)
         torch.cuda.synchronize()
         orth, res = metrics(q, r, a0)
-        out = {"config": "C3-cond", "m": m, "n": n, "cond": cond, "mode": mode, "orthogonality": orth, "residual": res}
+        out = {"config": "C3-uniform" if uniform else "C3-cond", "m": m, "n": n, "cond": cond, "mode": mode, "orthogonality": orth, "residual": res}
         if ref is not None:
             import math
             for reorth, tag in ((0, "reference"), (1, "reference_reorth")):   # mtk::qr::qr<mode, false / true>
