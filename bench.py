@@ -42,6 +42,18 @@ def parse():
     return ap.parse_args()
 
 
+def config_of(args, P):
+    """the same keys and wording for both arms (the driver compares them); the reference is single-GPU, so at
+    P > 1 its arm still factors one GPU's share"""
+    m, n = 1 << args.m_log2, args.n
+    esz = 2 if args.mode in ("fp16_notc", "fp16_tc_nocor") else 4
+    return {"workload": f"TSQR M=2^{args.m_log2} per GPU x N={n} {args.mode} "
+                        f"(mtk::qr::qr<{args.mode},{str(args.reorth).lower()}>), column-major, uniform(-1,1) generated on device",
+            "m_per_gpu": m, "m_total": m * P, "n": n, "mode": args.mode,
+            "parallelism": f"row-sharded x{P}, one all-gather of the {n}x{n} R factors" if P > 1 else "single GPU",
+            "l2": f"inputs ({m * n * esz / 2**30:.1f} GiB per GPU) are larger than the 126 MB L2; no flush needed"}
+
+
 def flops(m, n):
     return 4.0 * m * n * n - 4.0 / 3.0 * n ** 3
 
@@ -115,16 +127,16 @@ def cpu_lapack_baseline(n, budget_s=12.0):
     """multithreaded host LAPACK sgeqrf+sorgqr on a bounded sample of the same workload"""
     from oracle import oracle as o
     cores = len(os.sched_getaffinity(0))
-    m_s = 1 << 20
+    m_s = 1 << 22                     # BASELINE.md section 4.2: full size or a 2^22-row slab, labelled
     a = o.uniform_matrix(m_s, n, seed=1)
     o.lapack_qr(a[: 1 << 16])  # warm the library
     t0 = time.perf_counter(); o.lapack_qr(a); dt = time.perf_counter() - t0
     reps, total = 1, dt
-    while total < budget_s and reps < 4:
+    while total < budget_s and reps < 3:
         t0 = time.perf_counter(); o.lapack_qr(a); d = time.perf_counter() - t0
         total += d; reps += 1; dt = min(dt, d)
     return {"value": flops(m_s, n) / dt / 1e9, "unit": "GFLOP/s", "cores": cores, "kind": "port",
-            "sample": f"host LAPACK sgeqrf+sorgqr (scipy OpenBLAS) on M=2^20 x N={n} fp32 slab of the workload, "
+            "sample": f"host LAPACK sgeqrf+sorgqr (scipy OpenBLAS) on an M=2^22 x N={n} fp32 slab of the workload, "
                       f"best of {reps}, {dt * 1e3:.0f} ms"}
 
 
@@ -134,15 +146,16 @@ def run_reference(args, rank, world):
     rank 0 runs it on its GPU; if the build is missing, the host-LAPACK port is timed instead."""
     if rank != 0:
         return
-    import tsqr_gpu_b200 as tq
+    # nothing of this repo's product is imported or mapped in this arm: the helpers are local
+    modes = {"fp16_notc": 0, "fp16_tc_nocor": 1, "fp32_notc": 2, "fp32_tc_cor": 3, "fp32_tc_nocor": 4,
+             "mixed_tc_cor_emu": 5, "tf32_tc_cor": 6, "tf32_tc_cor_emu": 7, "tf32_tc_nocor": 8, "tf32_tc_nocor_emu": 9}
     m, n = 1 << args.m_log2, args.n
-    md = tq.MODES[args.mode]
+    md = modes[args.mode]
     so = os.path.join(ROOT, "oracle", "_ref", "libref_tcqr.so")
     base = {"impl": "reference", "metric": "tsqr_gflops", "unit": "GFLOP/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic"}
-    cfg = {"workload": f"TSQR M=2^{args.m_log2} N={n} {args.mode} (mtk::qr::qr<{args.mode},{str(args.reorth).lower()}>)",
-           "m": m, "n": n, "mode": args.mode}
+    cfg = config_of(args, 1)
     if not os.path.exists(so) or not torch.cuda.is_available():
         cb = cpu_lapack_baseline(n)
         cb["sample"] = "reference GPU build unavailable; " + cb["sample"]
@@ -153,10 +166,10 @@ def run_reference(args, rank, world):
     vp, sz = ctypes.c_void_p, ctypes.c_size_t
     lib.ref_gpu_qr.argtypes = [ctypes.c_int, ctypes.c_int, vp, sz, vp, sz, vp, sz, sz, sz, vp]
     lib.ref_gpu_qr.restype = ctypes.c_int
-    dt = tq.io_dtype(args.mode)
+    dt = torch.float16 if md in (0, 1) else torch.float32
     a0 = make_input(m, n, dt, 0x5EED0003)
-    a = tq.colmajor_empty(m, n, dt)
-    q = tq.colmajor_empty(m, n, dt)
+    a = torch.empty((n, m), dtype=dt, device="cuda").t()
+    q = torch.empty((n, m), dtype=dt, device="cuda").t()
     r = torch.zeros((n, n), dtype=dt, device="cuda").t()
     stream = torch.cuda.current_stream().cuda_stream
     times = []
@@ -257,11 +270,10 @@ def main():
     for i in range(cnt):
         per.setdefault(labels[i], []).append(dur[i])
     # (row-sharded runs also log the small root factorisation under the same labels: the slab's own
-    # level-0 launches are the `steps` longest ones)
-    top = lambda v: sorted(v)[-args.steps:] if v else [float("nan")]
-    t_reduce0 = float(np.mean(top(per.get(0, []))))
-    t_build0 = float(np.mean(top(per.get(1, []))))
-    t_upper = (sum(float(np.sum(v)) for v in per.values()) / max(args.steps, 1)) - t_reduce0 - t_build0
+    # launches are the `steps` longest ones of a label)
+    top = lambda v: sorted(v)[-args.steps:] if v else [0.0]
+    t_lab = {lb: float(np.mean(top(v))) for lb, v in per.items()}
+    t_all = sum(float(np.sum(v)) for v in per.values()) / max(args.steps, 1)
 
     # sanity of the result that was just timed: ||Q^T Q - I||_F / sqrt(n) (fp32 on device)
     orth_probe = None
@@ -329,19 +341,26 @@ def main():
         # store/load of the tensor-core path is implementation traffic, not algorithmic bytes.
         balg_reduce, balg_build = 1.0 * m * n * esz, 2.0 * m * n * esz
         tc = lib.tsqr_b200_mode_uses_tensor_cores(tq.MODES[args.mode], m) != 0 and n <= 64
-        kname = ("cs_reduce_kernel" if tc else "ts_pass_kernel<REDUCE>", "tc_build_kernel" if tc else "ts_pass_kernel<BUILD>")
-        if t_reduce0 >= t_build0:
-            dom = {"kernel": f"{kname[0]} level 0 (R-reduce pass: read A once" + (", write the reflectors V)" if tc else ")"),
-                   "bytes": balg_reduce, "ms": t_reduce0, "key": "reduce"}
-            others = {"build_level0": t_build0, "upper_levels_total": t_upper}
-        else:
-            dom = {"kernel": f"{kname[1]} level 0 (Q-build pass: read the slab, write Q)", "bytes": balg_build,
-                   "ms": t_build0, "key": "build"}
-            others = {"reduce_level0": t_reduce0, "upper_levels_total": t_upper}
+        # label -> (kernel, algorithmic bytes per launch): first pass reads A once, second pass reads it again
+        # and writes Q; anything else a kernel moves is implementation traffic
+        kernels = {
+            101: ("pc_pass_kernel<1> (Z = A R_pre^-1, Gram accumulation: read A once)", balg_reduce, "pc1"),
+            103: ("pc_pass_kernel<2> (Z again, Q = Z C: read A, write Q)", balg_build, "pc2"),
+            0: (("cs_reduce_kernel" if tc else "ts_pass_kernel<REDUCE>") + " level 0 (R-reduce pass: read A once)", balg_reduce, "reduce"),
+            1: (("tc_build_kernel" if tc else "ts_pass_kernel<BUILD>") + " level 0 (Q-build pass: read the slab, write Q)", balg_build, "build"),
+        }
+        dom_label = max(kernels, key=lambda lb: t_lab.get(lb, 0.0))
+        dom = {"kernel": kernels[dom_label][0], "bytes": kernels[dom_label][1], "ms": t_lab.get(dom_label, float("nan")),
+               "key": kernels[dom_label][2]}
+        names = {100: "pc_sample", 101: "pc_pass1", 102: "pc_finish", 103: "pc_pass2", 0: "householder_reduce_level0",
+                 1: "householder_build_level0"}
+        others = {names.get(lb, f"level{lb // 2}_{'build' if lb % 2 else 'reduce'}"): t for lb, t in sorted(t_lab.items())
+                  if lb != dom_label}
+        others["all_launches_total"] = t_all
         achieved = dom["bytes"] / (dom["ms"] * 1e-3) / 1e9
         traffic = None
         try:  # dram__bytes_read.sum + dram__bytes_write.sum of that kernel from the committed ncu capture
-            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
                 tr = json.load(f)
             traffic = tr.get(f"{dom['key']}:{args.mode}:m{args.m_log2}:n{n}")
         except Exception:
@@ -350,12 +369,7 @@ def main():
             "metric": "tsqr_gflops", "value": flops(m * P, n) / (ms * 1e-3) / 1e9, "unit": "GFLOP/s",
             "n_gpus": P, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"TSQR M=2^{args.m_log2} per GPU x N={n} {args.mode} "
-                                   f"(mtk::qr::qr<{args.mode},{str(args.reorth).lower()}> via the C ABI), column-major, "
-                                   "uniform(-1,1) generated on device",
-                       "m_per_gpu": m, "m_total": m * P, "n": n, "mode": args.mode,
-                       "parallelism": f"row-sharded x{P}, one all-gather of the {n}x{n} R factors" if P > 1 else "single GPU",
-                       "l2": f"inputs ({m * n * esz / 2**30:.1f} GiB per GPU) are larger than the 126 MB L2; no flush needed"},
+            "config": config_of(args, P),
             "hbm_gbs_per_gpu": balg_step / (ms * 1e-3) / 1e9,
             "hbm_frac_step": balg_step / (ms * 1e-3) / 1e9 / peak,
             "roofline": {"bound": "hbm", "kernel": dom["kernel"],

@@ -89,6 +89,20 @@ int tsqr_b200_profile_read(int* labels, float* ms, int capacity);
 int tsqr_b200_selftest_mma(int corrected, int variant, const float* A, const float* B, const float* X, float* D1,
                            float* D2, float* D3, float* D4, void* stream);
 
+/* The *_tc_* modes factor matrices of >= 16384 rows with the preconditioned-Cholesky passes (csrc/pc_tsqr.h)
+ * and fall back, on the device, to the Householder passes when the certificate of that path fails.
+ * tsqr_b200_pc_status: which of the two produced the last result held in `workspace` (the one passed to
+ * tsqr_b200_tsqr / tsqr_reduce for an m x n matrix in `mode`): 1 = fast path, 0 = Householder fallback,
+ * -1 = this (mode, m) never takes the fast path. Blocks on `stream`. *est (optional) receives the
+ * certificate value |G|_F |G^-1|_F / n. No reference counterpart. */
+int tsqr_b200_pc_status(int mode, size_t m, size_t n, const void* workspace, void* stream, float* est);
+/* Test probe of the two passes with caller-supplied factors (device pointers): pass 1 with R_pre = rpre
+ * (NP x NP float, ld NP, NP = n rounded up to 16/32/64) -> gsum (2 NP x NP doubles, row-major: rows [0, NP) =
+ * Z_hi^T Z_hi, rows [NP, 2 NP) = Z_lo^T Z_hi, Z = A rpre^-1); pass 2 with C = c -> q = Z c. */
+int tsqr_b200_pc_probe(int mode, const void* a, size_t lda, size_t m, size_t n, const float* rpre, const float* c,
+                       void* q, size_t ldq, double* gsum, int use_tma, void* workspace, size_t workspace_bytes,
+                       void* stream);
+
 /* how many kernels this library has launched in this process (bench bookkeeping) */
 unsigned long long tsqr_b200_launch_count(void);
 

@@ -164,3 +164,30 @@ def latms_matrix(m, n, cond, seed, dtype=np.float32):
     v, _ = np.linalg.qr(rng.standard_normal((n, n)))
     s = cond ** (-np.arange(n) / max(n - 1, 1))
     return np.asfortranarray(((u * s[None, :]) @ v.T).astype(dtype))
+
+
+def slatms_matrix(m, n, cond, iseed=(1, 2, 3, 5)):
+    """REAL LAPACK slatms (scipy's bundled OpenBLAS, symbol scipy_slatms_): MODE = 3 (geometric singular values
+    from 1 to 1/cond), DMAX = 1, full bandwidth, fixed ISEED -- the generator BASELINE.json's north_star names
+    ("latms-generated inputs"; the reference's own stand-in is src/latms.cu:8-121 + src/test_cond.cu:31-50)."""
+    import glob
+    import scipy
+    libs = glob.glob(os.path.join(os.path.dirname(os.path.dirname(scipy.__file__)), "scipy.libs", "libscipy_openblas*"))
+    if not libs:
+        raise RuntimeError("scipy's bundled OpenBLAS not found")
+    fn = ctypes.CDLL(libs[0]).scipy_slatms_
+    fn.restype = None
+    a = np.zeros((m, n), dtype=np.float32, order="F")
+    d = np.zeros(min(m, n), dtype=np.float32)
+    work = np.zeros(3 * max(m, n), dtype=np.float32)
+    seed = (ctypes.c_int * 4)(*iseed)                      # ISEED(4) must be odd
+    info = ctypes.c_int(0)
+    ci = lambda v: ctypes.byref(ctypes.c_int(v))
+    cf = lambda v: ctypes.byref(ctypes.c_float(v))
+    vp = lambda x: x.ctypes.data_as(ctypes.c_void_p)
+    one = ctypes.c_size_t(1)
+    fn(ci(m), ci(n), ctypes.c_char_p(b"N"), seed, ctypes.c_char_p(b"N"), vp(d), ci(3), cf(float(cond)), cf(1.0),
+       ci(m - 1), ci(n - 1), ctypes.c_char_p(b"N"), vp(a), ci(m), vp(work), ctypes.byref(info), one, one, one)
+    if info.value != 0:
+        raise RuntimeError(f"slatms failed: info = {info.value}")
+    return a

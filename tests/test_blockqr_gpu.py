@@ -77,3 +77,19 @@ def test_blockqr_tensor_core_nocor(cuda, oracle):
     for mode in ("fp32_tc_nocor", "tf32_tc_nocor", "fp16_tc_nocor"):
         q, r, a_in = run_qr(a, mode, True)
         assert oracle.orthogonality(q) < 5e-3 and oracle.residual(q, r, a_in) < 5e-3, mode
+
+
+@pytest.mark.parametrize("reorth", [False, True])
+def test_blockqr_tensor_core_wider_than_the_tmem_accumulators(cuda, oracle, reorth):
+    """n = 704: the projection of the last panels runs over 576 and 640 columns of Q1, more than the 8 accumulator
+    blocks (512 TMEM columns) one tc_tn_kernel launch holds; the driver must split Q1 into groups."""
+    from helpers import run_qr
+    a = oracle.uniform_matrix(4096, 704, seed=70)
+    q, r, a_in = run_qr(a, "fp32_tc_cor", reorth)
+    assert np.isfinite(q).all() and np.isfinite(r).all()
+    orth, res = oracle.orthogonality(q), oracle.residual(q, r, a_in)
+    print(f"4096x704 reorth={reorth}: orth {orth:.2e} res {res:.2e}")
+    assert res < 5e-6
+    assert orth < (5e-6 if reorth else 2e-4)
+    _, rl = oracle.lapack_qr(a_in, np.float64)
+    assert oracle.r_rel_diff(r, rl) < (3e-5 if reorth else 1e-3)

@@ -80,3 +80,27 @@ def test_latms_condition_number(oracle):
     a = oracle.latms_matrix(500, 16, 1e4, seed=1).astype(np.float64)
     s = np.linalg.svd(a, compute_uv=False)
     assert 0.5e4 < s[0] / s[-1] < 2e4
+
+
+def test_pc_tsqr_restatement_matches_lapack_quality(oracle):
+    """numpy restatement of the preconditioned-Cholesky path (oracle/pc_tsqr.py), fp32 arithmetic: LAPACK-class
+    orthogonality and residual whatever cond(A) is, and the certificate separates the inputs the sample
+    cannot represent."""
+    from oracle import pc_tsqr as pc
+    for a in (oracle.uniform_matrix(1 << 15, 64, seed=1), oracle.latms_matrix(1 << 15, 64, 1e6, seed=2),
+              oracle.uniform_matrix(20000, 7, seed=3), oracle.latms_matrix(1 << 15, 32, 1e4, seed=5)):
+        q, r, est, ok = pc.pc_tsqr(a)
+        assert ok and est < 2.0
+        q64, r64, a64 = q.astype(np.float64), r.astype(np.float64), a.astype(np.float64)
+        assert oracle.orthogonality(q64) < 5e-7 and oracle.residual(q64, r64, a64) < 5e-7
+        assert np.abs(np.tril(r64, -1)).max() == 0.0
+        _, rl = oracle.lapack_qr(a64, np.float64)
+        assert oracle.r_rel_diff(r64, rl) < 2e-5
+    m, n = 1 << 15, 64
+    bad = []
+    a = oracle.uniform_matrix(m, n, seed=9); a *= np.logspace(0, -8, m).astype(np.float32)[:, None]; bad.append(a)
+    a = oracle.uniform_matrix(m, n, seed=9); a[pc.sample_rows(m, n)] = 0.0; bad.append(a)
+    a = oracle.uniform_matrix(m, n, seed=9); a[:, 11] = 0.0; bad.append(a)
+    a = oracle.uniform_matrix(m, n, seed=9); a[:, 20] = a[:, 3]; bad.append(a)
+    for a in bad:
+        assert not pc.pc_tsqr(a)[3]

@@ -306,5 +306,36 @@ class HostPipeline:
         return r
 
 
+def pc_status(ws, m, n, mode):
+    """Which path produced the last TSQR result held in workspace `ws` (a uint8 tensor, or a Buffer):
+    (1, est) preconditioned-Cholesky fast path, (0, est) Householder fallback chosen on the device,
+    (-1, None) this (mode, m) never takes the fast path. Synchronises the current stream."""
+    ws = ws.ws if isinstance(ws, Buffer) else ws
+    est = ctypes.c_float(0.0)
+    code = lib.tsqr_b200_pc_status(_mode(mode), m, n, ws.data_ptr(), _stream(), ctypes.byref(est))
+    if code < -1:
+        _raise(code)
+    return code, (float(est.value) if code >= 0 else None)
+
+
+def pc_probe(a, mode, rpre, c, use_tma=True):
+    """tests: the two preconditioned-Cholesky passes with caller-supplied factors (see include/tsqr_b200.h).
+    Returns (q = (a rpre^-1) c, gsum (2 NP x NP float64, row-major))."""
+    md = _mode(mode)
+    m, n = a.shape
+    NP = 16 if n <= 16 else (32 if n <= 32 else 64)
+    lda = _check_colmajor(a, "a")
+    q = colmajor_empty(m, n, a.dtype, a.device)
+    gsum = torch.zeros((2 * NP, NP), dtype=torch.float64, device=a.device)
+    ws = torch.empty(lib.tsqr_b200_tsqr_workspace_bytes(m, n), dtype=torch.uint8, device=a.device)
+    assert rpre.shape == (NP, NP) and c.shape == (NP, NP) and rpre.dtype == torch.float32 and c.dtype == torch.float32
+    rp = to_colmajor(rpre)
+    cc = to_colmajor(c)
+    code = lib.tsqr_b200_pc_probe(md, a.data_ptr(), lda, m, n, rp.data_ptr(), cc.data_ptr(), q.data_ptr(), m,
+                                  gsum.data_ptr(), 1 if use_tma else 0, ws.data_ptr(), ws.numel(), _stream())
+    _raise(code)
+    return q, gsum
+
+
 def launch_count():
     return int(lib.tsqr_b200_launch_count())

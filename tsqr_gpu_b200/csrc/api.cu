@@ -9,6 +9,7 @@
 #include "small_qr.h"
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
 
@@ -130,6 +131,36 @@ int tsqr_b200_tsqr_build(int mode, void* q, size_t ldq, const void* a, size_t ld
   });
 }
 
+int tsqr_b200_pc_probe(int mode, const void* a, size_t lda, size_t m, size_t n, const float* rpre, const float* c,
+                       void* q, size_t ldq, double* gsum, int use_tma, void* ws, size_t ws_bytes, void* stream) {
+  if (!mode_valid(mode) || !mode_is_tc(mode)) { set_err("the probe takes a *_tc_* mode"); return TSQR_B200_ERR_ARGUMENT; }
+  if (m == 0 || n == 0 || n > (size_t)kMaxN) return TSQR_B200_INVALID_SIZE;
+  return guarded([&] {
+    PcCall call{};
+    call.A = a; call.lda = (long long)lda; call.M = (long long)m; call.n = (int)n;
+    call.Q = q; call.ldq = (long long)ldq;
+    call.io = mode_io(mode); call.cor = mode_is_cor(mode);
+    call.ws = (float*)ws; call.L = pc_layout((long long)m, (int)n);
+    if (call.L.total * sizeof(float) > ws_bytes) throw std::runtime_error("tsqr_b200: workspace too small");
+    pc_probe(call, rpre, c, gsum, use_tma != 0, (cudaStream_t)stream);
+    return 0;
+  });
+}
+
+int tsqr_b200_pc_status(int mode, size_t m, size_t n, const void* ws, void* stream, float* est) {
+  if (!mode_valid(mode) || m == 0 || n == 0 || n > (size_t)kMaxN) return -1;
+  if (!use_pc(mode, (long long)m)) return -1;
+  return guarded([&] {
+    Plan plan = make_plan_for(mode, (long long)m, (int)n);
+    int st[4] = {0, 0, 0, 0};
+    TSQR_CUDA_CHECK(cudaMemcpyAsync(st, (const float*)ws + plan.pc_off + plan.pcl.status, sizeof(st), cudaMemcpyDeviceToHost,
+                                    (cudaStream_t)stream));
+    TSQR_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+    if (est) std::memcpy(est, &st[2], sizeof(float));
+    return st[0] == kPcOk ? 1 : 0;
+  });
+}
+
 int tsqr_b200_qr32x16_batched(int mode, void* q, size_t ldq, void* r, size_t ldr, const void* a, size_t lda,
                               unsigned m, unsigned n, size_t batch, const unsigned* starts, void* stream) {
   if (!mode_valid(mode)) { set_err("invalid compute mode"); return TSQR_B200_ERR_ARGUMENT; }
@@ -149,6 +180,13 @@ int tsqr_b200_qr32x16_batched(int mode, void* q, size_t ldq, void* r, size_t ldr
 
 // ------------------------------------------------------------------ mtk:: C++ API
 namespace {
+// The reference's entries return after a stream synchronisation (src/blockqr.cu:140, src/tsqr.cu:1260) and its own
+// driver times them with a wall clock and no sync (src/test.cu:299-309). The mtk:: entries keep that contract;
+// TSQR_B200_ASYNC=1 opts out (the C ABI is always asynchronous).
+bool cxx_blocking() {
+  static const bool b = [] { const char* e = std::getenv("TSQR_B200_ASYNC"); return !(e && e[0] == '1'); }();
+  return b;
+}
 // All workspace lives in the `wq` array. Its element count is sized for 2-byte elements
 // (see get_working_q_size), so the byte capacity is at least count * 2 for every mode.
 size_t wq_capacity_bytes_qr(size_t m, size_t n) { return mtk::qr::get_working_q_size(m, n) * 2; }
@@ -190,6 +228,7 @@ void mtk::tsqr::tsqr16(typename mtk::tsqr::get_io_type<mode>::type* const q_ptr,
   if (n > (std::size_t)kMaxN) throw std::runtime_error("tsqr_b200: tsqr16 takes n <= 64");
   tsqr_full((int)mode, q_ptr, (long long)ldq, r_ptr, (long long)ldr, a_ptr, (long long)lda, (long long)m, (int)n,
             reinterpret_cast<float*>(working_q_ptr), wq_capacity_bytes_tsqr(m, n), cuda_stream);
+  if (cxx_blocking()) TSQR_CUDA_CHECK(cudaStreamSynchronize(cuda_stream));
 }
 
 template <mtk::qr::compute_mode mode, bool Reorthogonalize>
@@ -202,9 +241,11 @@ mtk::qr::state_t mtk::qr::qr(typename mtk::qr::get_io_type<mode>::type* const q_
                              typename mtk::qr::get_io_type<mode>::type* const, unsigned* const, unsigned* const,
                              cublasHandle_t const main_cublas_handle) {
   if (n > m || m == 0 || n == 0) return mtk::qr::error_invalid_matrix_size;
-  return qr_full((int)mode, Reorthogonalize, q_ptr, (long long)ldq, r_ptr, (long long)ldr, a_ptr, (long long)lda,
-                 (long long)m, (long long)n, reinterpret_cast<float*>(wq_ptr), wq_capacity_bytes_qr(m, n),
-                 stream_of(main_cublas_handle));
+  cudaStream_t const stream = stream_of(main_cublas_handle);
+  const int st = qr_full((int)mode, Reorthogonalize, q_ptr, (long long)ldq, r_ptr, (long long)ldr, a_ptr, (long long)lda,
+                         (long long)m, (long long)n, reinterpret_cast<float*>(wq_ptr), wq_capacity_bytes_qr(m, n), stream);
+  if (cxx_blocking()) TSQR_CUDA_CHECK(cudaStreamSynchronize(stream));
+  return st;
 }
 
 template <mtk::tcqr::compute_mode mode, class Q_T, class R_T, class A_T>

@@ -11,6 +11,7 @@ namespace {
 
 constexpr int kNB = kMaxN;     // panel width
 constexpr int kSlabRows = 32;  // rows staged per step in the T-N product
+constexpr int kTcProjectMaxK = 512;   // columns of Q1 one tc_tn_kernel launch can hold (8 accumulator blocks of 64 TMEM columns)
 
 // Cp[slab][i + k*kb] = sum over the slab's rows of X[row, i] * Y[row, k]   (i < kb, k < nb)
 template <typename T>
@@ -147,7 +148,7 @@ __global__ void store_rcol(const float* Rcol, int ldrc, int kb, int nb, T* R, lo
 }
 
 struct QrWs {
-  size_t tsqr_off, cp_off, c_off, s_off, rcol_off, w_off, total;
+  size_t tsqr_off, cp_off, c_off, s_off, rcol_off, w_off, cg_off, total;
   int nslabs;
   long long rows_per_slab;
 };
@@ -169,6 +170,7 @@ QrWs carve(long long m, long long n, bool reorth) {
     w.s_off = take(reorth ? (size_t)kbmax * kNB : 0);
     w.rcol_off = take((size_t)n * kNB);
     w.w_off = take((size_t)kNB * kNB * 2);
+    w.cg_off = take(kbmax > kTcProjectMaxK ? (size_t)kTcProjectMaxK * kNB : 0);
   }
   w.total = off;
   return w;
@@ -183,8 +185,24 @@ template <typename T>
 void project(int mode, const T* Q1, long long ldq, int kb, T* Y, long long ldy, int nb, long long m, const QrWs& w, float* ws,
              float* Cout, cudaStream_t s) {
   if (use_tc(mode, m)) {  // tcgen05 path: both GEMMs on the tensor cores
-    launch_tc_project(mode_is_cor(mode), sizeof(T) == 2 ? IoType::f16 : IoType::f32, Q1, ldq, kb, Y, ldy, nb, m, w.nslabs,
-                      w.rows_per_slab, ws + w.cp_off, Cout, reduce_partials_launch, s);
+    const IoType io = sizeof(T) == 2 ? IoType::f16 : IoType::f32;
+    if (kb <= kTcProjectMaxK) {
+      launch_tc_project(mode_is_cor(mode), io, Q1, ldq, kb, Y, ldy, nb, m, w.nslabs, w.rows_per_slab, ws + w.cp_off, Cout,
+                        reduce_partials_launch, s);
+      return;
+    }
+    // The tn kernel keeps one 64-column accumulator block per 64 columns of Q1 in its 512 TMEM columns: wider
+    // Q1 goes through in groups of 512 columns, each group projected out of Y before the next one is measured
+    // (block Gram-Schmidt across the groups; A2 = sum_g Q1_g C_g + Y' holds exactly as before).
+    float* Cg = ws + w.cg_off;
+    for (int g0 = 0; g0 < kb; g0 += kTcProjectMaxK) {
+      const int kg = std::min(kTcProjectMaxK, kb - g0);
+      launch_tc_project(mode_is_cor(mode), io, Q1 + (long long)g0 * ldq, ldq, kg, Y, ldy, nb, m, w.nslabs, w.rows_per_slab,
+                        ws + w.cp_off, Cg, reduce_partials_launch, s);
+      copy_block<<<(kg * nb + 255) / 256, 256, 0, s>>>(Cg, kg, Cout + g0, kb, kg, nb);
+      note_launch();
+    }
+    TSQR_CUDA_CHECK(cudaGetLastError());
     return;
   }
   dim3 grid(w.nslabs, (kb + 63) / 64);

@@ -39,9 +39,9 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f
 // raw element loads: the conversion of fp16 input is kept apart from the load so that a whole batch of
 // loads is in flight before the first use (with __half2float(__ldg(p)) the compiler reuses one register
 // for load + convert and serialises the batch)
-__device__ __forceinline__ float raw_load(const float* p) { return __ldg(p); }
+__device__ __forceinline__ float raw_load(const float* p) { return *p; }   // plain load: A may alias Q, which this kernel writes
 __device__ __forceinline__ unsigned short raw_load(const __half* p) {
-  unsigned short v; asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(v) : "l"(p)); return v;
+  unsigned short v; asm volatile("ld.global.u16 %0, [%1];" : "=h"(v) : "l"(p)); return v;
 }
 __device__ __forceinline__ float raw_cvt(float v) { return v; }
 __device__ __forceinline__ float raw_cvt(unsigned short v) { return __half2float(__ushort_as_half(v)); }
@@ -221,6 +221,7 @@ __global__ void __launch_bounds__(CL * RS, MINB) cs_reduce_kernel(const TcParams
   using L = CsSmem<NP, RS, CL>;
   constexpr int LD = L::LD, KP = NP / CL, kT = CL * RS, RPT = kTileRows / RS, NI = RPT / 2, RT = kTileRows / kT;
   extern __shared__ __align__(128) char sm[];
+  if (P.skip_ok && *P.skip_ok == kPcOk) return;
   float* tileS = reinterpret_cast<float*>(sm + L::oTile);
   float* Rs = reinterpret_cast<float*>(sm + L::oR);
   float* part = reinterpret_cast<float*>(sm + L::oPart);
@@ -239,7 +240,7 @@ __global__ void __launch_bounds__(CL * RS, MINB) cs_reduce_kernel(const TcParams
     for (int idx = t; idx < NP * NP; idx += kT) {
       const int r = idx % NP, c = idx / NP;
       const long long row = cbeg + r;
-      Hs[c * LD + r] = (row < cend && c < n) ? io_load(A + row + (long long)c * P.lda) : 0.f;
+      Hs[c * LD + r] = (row < cend && c < n) ? io_plain(A + row + (long long)c * P.lda) : 0.f;
     }
     __syncthreads();
     // Column c lives in the registers of thread c (fully unrolled steps, compile-time row indices);

@@ -1,6 +1,7 @@
 #include "driver.h"
 #include "common.cuh"
 #include <algorithm>
+#include <atomic>
 #include <cstdlib>
 #include <mutex>
 
@@ -24,21 +25,31 @@ int device_sm_count() {
 
 namespace {
 struct ProfRec { int label; cudaEvent_t beg, end; };
-bool g_prof_on = false;
+std::atomic<bool> g_prof_on{false};
 std::vector<ProfRec> g_prof;
+std::vector<cudaEvent_t> g_prof_pool;   // events are recycled: none is created inside a timed region twice
 std::mutex g_prof_mu;
-struct ProfScope {
-  cudaStream_t s; int label; cudaEvent_t beg = nullptr, end = nullptr; bool on;
-  ProfScope(cudaStream_t st, int lb) : s(st), label(lb), on(g_prof_on) {
-    if (on) { cudaEventCreate(&beg); cudaEventCreate(&end); cudaEventRecord(beg, s); }
-  }
-  ~ProfScope() {
-    if (on) { cudaEventRecord(end, s); std::lock_guard<std::mutex> lk(g_prof_mu); g_prof.push_back({label, beg, end}); }
-  }
-};
+cudaEvent_t prof_event() {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
 }  // namespace
+ProfScope::ProfScope(cudaStream_t st, int lb) : s(st), label(lb), on(g_prof_on.load(std::memory_order_relaxed)) {
+  if (on) { beg = prof_event(); end = prof_event(); cudaEventRecord(beg, s); }
+}
+ProfScope::~ProfScope() {
+  if (on) {
+    cudaEventRecord(end, s);
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    if (g_prof.size() < 65536) g_prof.push_back({label, beg, end});
+    else { g_prof_pool.push_back(beg); g_prof_pool.push_back(end); }
+  }
+}
 
-void profile_enable(bool on) { g_prof_on = on; }
+void profile_enable(bool on) { g_prof_on.store(on); }
 int profile_read(int* labels, float* ms, int cap) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
   int n = 0;
@@ -47,7 +58,7 @@ int profile_read(int* labels, float* ms, int cap) {
     cudaEventSynchronize(r.end);
     cudaEventElapsedTime(&t, r.beg, r.end);
     if (n < cap) { labels[n] = r.label; ms[n] = t; ++n; }
-    cudaEventDestroy(r.beg); cudaEventDestroy(r.end);
+    g_prof_pool.push_back(r.beg); g_prof_pool.push_back(r.end);
   }
   g_prof.clear();
   return n;
@@ -139,8 +150,26 @@ Plan make_plan(long long m, int n, int max_chunks0, bool tc) {
   return plan;
 }
 
+bool pc_enabled() {
+  static const bool on = [] { const char* e = std::getenv("TSQR_B200_PC"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
+Plan make_plan_for(int mode, long long m, int n) {
+  Plan plan = make_plan(m, n, 0, use_tc(mode, m));
+  if (use_pc(mode, m)) {
+    plan.pc = true;
+    plan.pc_off = align_up(plan.total_floats, 64);
+    plan.pcl = pc_layout(m, n);
+    plan.total_floats = plan.pc_off + plan.pcl.total;
+  }
+  return plan;
+}
+
 size_t plan_floats_any(long long m, int n) {
-  return std::max(make_plan(m, n, 0, false).total_floats, make_plan(m, n, 0, true).total_floats);
+  size_t tcf = make_plan(m, n, 0, true).total_floats;
+  if (m >= kPcMinRows) tcf = align_up(tcf, 64) + pc_layout(m, n).total;
+  return std::max(make_plan(m, n, 0, false).total_floats, tcf);
 }
 
 size_t tsqr_workspace_bytes(long long m, int n) { return plan_floats_any(m, n) * sizeof(float) + 256; }
@@ -185,18 +214,38 @@ static PassParams level_params(const Plan& plan, size_t li, const void* a, long 
   return p;
 }
 
+static PcCall pc_call(const Plan& plan, int mode, const void* a, long long lda, void* q, long long ldq, float* ws) {
+  PcCall c{};
+  c.A = a; c.lda = lda; c.M = plan.m; c.n = plan.n;
+  c.Q = q; c.ldq = ldq;
+  c.io = mode_io(mode);
+  c.cor = mode_is_cor(mode);
+  c.ws = ws + plan.pc_off;
+  c.L = plan.pcl;
+  return c;
+}
+
 const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long lda, void* q, long long ldq, float* ws,
                          cudaStream_t s) {
   if (plan.tc) {
+    const int* skip = nullptr;
+    float* rout = nullptr;
+    if (plan.pc) {   // fast path first; the levels below return at once when its certificate passed
+      pc_reduce(pc_call(plan, mode, a, lda, q, ldq, ws), s);
+      skip = reinterpret_cast<const int*>(ws + plan.pc_off + plan.pcl.status);
+      rout = ws + plan.pc_off + plan.pcl.rout;
+    }
     for (size_t li = 0; li < plan.levels.size(); ++li) {
       TcParams p = tc_level_params(plan, li, a, lda, q, ldq, ws);
+      p.skip_ok = skip;
+      if (rout && li + 1 == plan.levels.size()) { p.S = rout; p.lds = plan.n; }   // one home for R, whoever wrote it
       ProfScope prof(s, (int)li * 2);
       const IoType io = li == 0 ? mode_io(mode) : IoType::f32;
       static const bool use_tc_reduce = [] { const char* e = std::getenv("TSQR_B200_REDUCE"); return e && e[0] == 't'; }();
       if (use_tc_reduce) launch_tc_reduce(p, mode_is_cor(mode), io, io, s);
       else launch_cs_reduce(p, io, io, s);
     }
-    return ws + plan.levels.back().S_off;
+    return rout ? rout : ws + plan.levels.back().S_off;
   }
   for (size_t li = 0; li < plan.levels.size(); ++li) {
     PassParams p = level_params(plan, li, a, lda, ws);
@@ -209,9 +258,16 @@ const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long ld
 void tsqr_build(const Plan& plan, int mode, const void* a, long long lda, void* q, long long ldq,
                 const float* B, long long ldb, float* ws, cudaStream_t s) {
   if (plan.tc) {
+    const int* skip = nullptr;
+    if (plan.pc) {
+      ProfScope prof(s, 103);
+      pc_build(pc_call(plan, mode, a, lda, q, ldq, ws), B, ldb, s);
+      skip = reinterpret_cast<const int*>(ws + plan.pc_off + plan.pcl.status);
+    }
     for (size_t li = plan.levels.size(); li-- > 0;) {
       const Level& L = plan.levels[li];
       TcParams p = tc_level_params(plan, li, a, lda, q, ldq, ws);
+      p.skip_ok = skip;
       ProfScope prof(s, (int)li * 2 + 1);
       if (li + 1 == plan.levels.size()) { p.Bsrc = B; p.ldb = ldb; }
       else { p.Bsrc = ws + L.Qup_off; p.ldb = (long long)L.nchunks * plan.n; }

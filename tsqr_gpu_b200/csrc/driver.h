@@ -6,6 +6,7 @@
 #include <cstddef>
 #include <vector>
 #include "ts_pass.h"
+#include "pc_tsqr.h"
 
 namespace tsqr_b200 {
 
@@ -31,6 +32,10 @@ struct Level {
 
 struct Plan {
   bool tc = false;  // tensor-core passes (TcParams chunk format) instead of the CUDA-core passes
+  bool pc = false;  // preconditioned-Cholesky fast path first (pc_tsqr.h); the tensor-core Householder levels
+                    // below are enqueued behind it and return at once unless its certificate failed
+  size_t pc_off = 0;   // float offset of the PC region in the workspace
+  PcLayout pcl;
   long long m;
   int n, np;
   std::vector<Level> levels;
@@ -40,7 +45,13 @@ struct Plan {
 int device_sm_count();
 
 // Optional per-launch timing of the level passes (CUDA events on the launching stream, read
-// back after the caller synchronised). label = level * 2 + (build ? 1 : 0).
+// back after the caller synchronised). label = level * 2 + (build ? 1 : 0) for the Householder levels,
+// 100 = PC sample, 101 = PC pass 1, 102 = PC finish, 103 = PC pass 2 (with its C product).
+struct ProfScope {
+  cudaStream_t s; int label; cudaEvent_t beg = nullptr, end = nullptr; bool on;
+  ProfScope(cudaStream_t st, int lb);
+  ~ProfScope();
+};
 void profile_enable(bool on);
 int profile_read(int* labels, float* ms, int cap);  // returns #records copied, clears them
 // levels for an m x n TSQR (n <= kMaxN). max_chunks0 <= 0 picks 1 CTA wave per SM x occupancy.
@@ -50,7 +61,9 @@ inline bool mode_is_tc(int m) { return m == fp16_tc_nocor || m == fp32_tc_cor ||
 inline bool mode_is_cor(int m) { return m == fp32_tc_cor || m == tf32_tc_cor; }
 constexpr long long kTcMinRows = 1024;
 inline bool use_tc(int mode, long long m) { return mode_is_tc(mode) && m >= kTcMinRows; }
-inline Plan make_plan_for(int mode, long long m, int n) { return make_plan(m, n, 0, use_tc(mode, m)); }
+bool pc_enabled();   // TSQR_B200_PC=0 switches the fast path off (Householder passes only)
+inline bool use_pc(int mode, long long m) { return mode_is_tc(mode) && m >= kPcMinRows && pc_enabled(); }
+Plan make_plan_for(int mode, long long m, int n);
 // workspace floats that cover every mode's plan
 size_t plan_floats_any(long long m, int n);
 size_t tsqr_workspace_bytes(long long m, int n);

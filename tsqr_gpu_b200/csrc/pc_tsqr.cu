@@ -1,0 +1,803 @@
+// Preconditioned-Cholesky TSQR for sm_100a (see pc_tsqr.h for the algorithm).
+//
+// Kernels (one CTA = 128 threads = one 128-row tile at a time, thread t = tile row t = TMEM lane t):
+//   pc_sample_kernel : h = 8 NP strided rows of A -> R_pre (Householder sweep in the (column, row-segment)
+//                      register layout of cs_reduce.cu, column norms / reflector dots by shuffles)
+//   pc_pass_kernel<1>: TMA tile -> registers; Z = A R_pre^-1 panel by panel: 16 x 16 diagonal solves on
+//                      CUDA cores (no cross-thread traffic: a row of Z depends on its own row of A only),
+//                      off-diagonal updates U += Z_p R[p, trail] on tcgen05 with the A operand READ FROM
+//                      TENSOR MEMORY (tcgen05.st by the row's thread, hi/lo split fused into the store) and
+//                      the R blocks as shared-memory B operands; G_tile = [Z_hi | Z_lo]^T Z_hi as one
+//                      M = 128 product on 128-byte-swizzled K-major operands; fp32 -> fp64 accumulation
+//   pc_finish_kernel : sum of the CTA partials, chol, certificate, R = R_z R_pre, C = R_z^-1 (fp64)
+//   pc_pass_kernel<2>: Z again, Q_tile = Z C on tcgen05 (A operand from tensor memory), Q stored
+// Replaces, for the tensor-core modes, reference src/tcqr32x16.cu:1373-1469 (leaf QR), src/tsqr.cu:1102-1172
+// (R tree) and src/tsqr.cu:143-1061 (backward products).
+#include <cuda.h>
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include "common.cuh"
+#include "tc05.cuh"
+#include "pc_tsqr.h"
+#include "driver.h"
+
+namespace tsqr_b200 {
+namespace {
+using namespace tc;
+
+constexpr unsigned kFull = 0xffffffffu;
+
+struct PcParams {
+  const void* A; long long lda; long long M; int n;
+  void* Q; long long ldq;
+  const float* Rpre;     // NP x NP, ld NP, upper, identity-padded beyond n
+  const float* C;        // pass 2
+  double* Gpart;         // pass 1
+  int* status;
+  int tiles, tiles_per_cta, use_tma;
+};
+
+__device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rsqrt_approx(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
+// ======================================================================================= sample
+// Householder QR of the h x NP sample with structured reflectors [e_j ; v_j] on top of a zero R (only R is
+// wanted: it is a preconditioner, the Cholesky step absorbs whatever it misses). Thread (cl = t % 16,
+// s = t / 16) owns rows [16 s, 16 s + 16) of the columns cl + 16 k.
+struct HhScal { float beta, tau, rden; };
+__device__ __forceinline__ HhScal hh_scalars(float alpha, float g) {
+  HhScal h;
+  const float nx2 = __fmaf_rn(alpha, alpha, g);
+  const bool ok = nx2 > 1e-36f;
+  const float nx2s = ok ? nx2 : 1.f;
+  const float y = rsqrt_approx(nx2s);
+  const float n0 = __fmul_rn(nx2s, y);
+  const float norm = __fmaf_rn(__fmul_rn(0.5f, y), __fmaf_rn(-n0, n0, nx2s), n0);
+  const float beta = -copysignf(norm, alpha);
+  h.beta = ok ? beta : 0.f;
+  h.rden = ok ? rcp_approx(__fsub_rn(alpha, beta)) : 0.f;
+  h.tau = ok ? __fmaf_rn(fabsf(alpha), rcp_approx(norm), 1.f) : 2.f;
+  return h;
+}
+template <int NW>
+__device__ __forceinline__ float part_sum(const float* p) {
+  float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int i = 0; i < NW; i += 4) {
+    const float4 v = *reinterpret_cast<const float4*>(p + i);
+    s0 = __fadd_rn(s0, __fadd_rn(v.x, v.y));
+    s1 = __fadd_rn(s1, __fadd_rn(v.z, v.w));
+  }
+  return __fadd_rn(s0, s1);
+}
+
+template <int NP>
+struct SmpCfg {
+  static constexpr int H = 8 * NP, T = 8 * NP, NW = T / 32, PS = H + 4, LD = NP + 1, KP = NP / 16;
+  static constexpr uint32_t oTile = 0;
+  static constexpr uint32_t oR = oTile + NP * PS * 4;
+  static constexpr uint32_t oPart = oR + NP * LD * 4;
+  static constexpr uint32_t kBytes = oPart + 2 * NP * NW * 4 + 16;
+};
+
+template <int PJ, int NP>
+__device__ __forceinline__ void smp_sweep_panel(f32x2 (&a)[NP / 16][8], float* tileS, float* Rs, float* part, int t) {
+  using Cf = SmpCfg<NP>;
+  constexpr int KP = Cf::KP, NW = Cf::NW, PS = Cf::PS, LD = Cf::LD, K0 = PJ;
+  const int cl = t & 15, s = t >> 4, lane = t & 31, warp = t >> 5;
+#pragma unroll 1
+  for (int jl = 0; jl < 16; ++jl) {
+    const int j = 16 * PJ + jl;
+    __syncwarp();  // column j of this row segment was published by a lane of the same half warp
+    f32x2 vj[8];
+    {
+      const ulonglong2* src = reinterpret_cast<const ulonglong2*>(tileS + j * PS + 16 * s);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { const ulonglong2 v = src[i]; vj[2 * i] = v.x; vj[2 * i + 1] = v.y; }
+    }
+    const float alpha = Rs[j * LD + j];
+    float rjc[KP];
+#pragma unroll
+    for (int k = K0; k < KP; ++k) rjc[k] = Rs[j * LD + cl + 16 * k];
+    float* pb = part + (jl & 1) * (NP * NW);
+#pragma unroll
+    for (int k = K0; k < KP; ++k) {
+      f32x2 q0 = 0ull, q1 = 0ull;
+#pragma unroll
+      for (int i = 0; i < 8; i += 2) { q0 = fma2(vj[i], a[k][i], q0); q1 = fma2(vj[i + 1], a[k][i + 1], q1); }
+      float p0, p1, p2, p3;
+      unpack2(q0, p0, p1);
+      unpack2(q1, p2, p3);
+      float p = __fadd_rn(__fadd_rn(p0, p1), __fadd_rn(p2, p3));
+      p = __fadd_rn(p, __shfl_xor_sync(kFull, p, 16));
+      if (lane < 16) pb[(cl + 16 * k) * NW + warp] = p;
+    }
+    __syncthreads();
+    const HhScal h = hh_scalars(alpha, part_sum<NW>(pb + j * NW));
+#pragma unroll
+    for (int k = K0; k < KP; ++k) {
+      const int c = cl + 16 * k;
+      const float g = part_sum<NW>(pb + c * NW);
+      const float coef = __fmul_rn(h.tau, __fmaf_rn(g, h.rden, rjc[k]));
+      const bool active = (k > K0) || (cl > jl);
+      const float ncv = active ? -__fmul_rn(coef, h.rden) : 0.f;
+      const f32x2 ncv2 = pack2(ncv, ncv);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a[k][i] = fma2(ncv2, vj[i], a[k][i]);
+      if (s == 0 && active) Rs[j * LD + c] = __fsub_rn(rjc[k], coef);
+    }
+    if (jl < 15 && cl == jl + 1) {  // publish the next pivot column of this panel
+      ulonglong2* dst = reinterpret_cast<ulonglong2*>(tileS + (j + 1) * PS + 16 * s);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dst[i] = make_ulonglong2(a[K0][2 * i], a[K0][2 * i + 1]);
+    }
+    if (s == 0 && cl == jl) Rs[j * LD + j] = h.beta;
+  }
+  if (PJ + 1 < KP) {  // first pivot column of the next panel
+    constexpr int K1 = PJ + 1 < KP ? PJ + 1 : 0;
+    if (cl == 0) {
+      ulonglong2* dst = reinterpret_cast<ulonglong2*>(tileS + (16 * K1) * PS + 16 * s);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dst[i] = make_ulonglong2(a[K1][2 * i], a[K1][2 * i + 1]);
+    }
+  }
+}
+template <int PJ, int NP>
+struct SmpSweepAll {
+  static __device__ __forceinline__ void run(f32x2 (&a)[NP / 16][8], float* tileS, float* Rs, float* part, int t) {
+    smp_sweep_panel<PJ, NP>(a, tileS, Rs, part, t);
+    SmpSweepAll<PJ + 1, NP>::run(a, tileS, Rs, part, t);
+  }
+};
+template <int NP>
+struct SmpSweepAll<NP / 16, NP> {
+  static __device__ __forceinline__ void run(f32x2 (&)[NP / 16][8], float*, float*, float*, int) {}
+};
+
+template <int NP, typename TIo>
+__global__ void __launch_bounds__(8 * NP, 1) pc_sample_kernel(const TIo* __restrict__ A, long long lda, long long M, int n,
+                                                             float* __restrict__ Rpre, int* __restrict__ status) {
+  using Cf = SmpCfg<NP>;
+  constexpr int H = Cf::H, T = Cf::T, PS = Cf::PS, LD = Cf::LD, KP = Cf::KP;
+  extern __shared__ __align__(128) char sm[];
+  float* tileS = reinterpret_cast<float*>(sm + Cf::oTile);
+  float* Rs = reinterpret_cast<float*>(sm + Cf::oR);
+  float* part = reinterpret_cast<float*>(sm + Cf::oPart);
+  const int t = threadIdx.x, cl = t & 15, s = t >> 4;
+  if (t == 0) { status[0] = 0; status[1] = 0; }
+  {
+    const long long row = ((long long)t * M) / H;   // sample row t of H, evenly spread over the matrix
+    const TIo* ap = A + row;
+#pragma unroll 8
+    for (int c = 0; c < NP; ++c) tileS[c * PS + t] = (c < n) ? io_load(ap + (long long)c * lda) : 0.f;
+  }
+  for (int i = t; i < NP * LD; i += T) Rs[i] = 0.f;
+  __syncthreads();
+  f32x2 a[KP][8];
+#pragma unroll
+  for (int k = 0; k < KP; ++k) {
+    const ulonglong2* src = reinterpret_cast<const ulonglong2*>(tileS + (cl + 16 * k) * PS + 16 * s);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const ulonglong2 v = src[i]; a[k][2 * i] = v.x; a[k][2 * i + 1] = v.y; }
+  }
+  SmpSweepAll<0, NP>::run(a, tileS, Rs, part, t);
+  __syncthreads();
+  for (int i = t; i < NP * NP; i += T) {
+    const int k = i % NP, c = i / NP;
+    float v = 0.f;
+    if (k < n && c < n) v = (k <= c) ? Rs[k * LD + c] : 0.f;
+    else if (k == c) v = 1.f;
+    Rpre[k + c * NP] = v;
+  }
+}
+
+// ======================================================================================= passes
+template <int NP>
+__host__ __device__ constexpr uint32_t rblk_off(int p) {   // byte offset of R block p (rows [16p, 16p+16), cols >= 16(p+1))
+  uint32_t o = 0;
+  for (int q = 0; q < p; ++q) o += kb::bytes(16, NP - 16 * (q + 1));
+  return o;
+}
+template <int NP, int PASS>
+struct PassSmem {
+  static constexpr int NPAN = NP / 16;
+  static constexpr uint32_t oLand = 0;                                                  // 128 x NP io elements
+  static constexpr uint32_t oBig = 32768;                                               // Gram operand | C hi, C lo
+  static constexpr uint32_t kBig = PASS == 1 ? sw::bytes(128) : 2 * kb::bytes(NP, NP);
+  static constexpr uint32_t kRblk = rblk_off<NP>(NPAN - 1);
+  static constexpr uint32_t oRblkHi = oBig + kBig;
+  static constexpr uint32_t oRblkLo = oRblkHi + kRblk;
+  static constexpr uint32_t oRd = oRblkLo + kRblk;                                      // -R diagonal blocks, [NP][16]
+  static constexpr uint32_t oRinv = oRd + NP * 16 * 4;
+  static constexpr uint32_t oBar = oRinv + NP * 4;                                      // 3 mbarriers, tmem slot
+  static constexpr uint32_t kBytes = oBar + 64;
+};
+
+template <int NP, bool COR, typename TIo, int PASS>
+__global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const __grid_constant__ CUtensorMap tmapA) {
+  using Sm = PassSmem<NP, PASS>;
+  constexpr int NPAN = NP / 16;
+  extern __shared__ __align__(1024) char sm[];
+  if (PASS == 2 && *P.status != kPcOk) return;   // the Householder passes behind this launch do the work
+  const int t = threadIdx.x, warp = t >> 5;
+  TIo* land = reinterpret_cast<TIo*>(sm + Sm::oLand);
+  char* big = sm + Sm::oBig;
+  char* RbHi = sm + Sm::oRblkHi;
+  char* RbLo = sm + Sm::oRblkLo;
+  float* Rd = reinterpret_cast<float*>(sm + Sm::oRd);
+  float* rinv = reinterpret_cast<float*>(sm + Sm::oRinv);
+  uint64_t* bar_full = reinterpret_cast<uint64_t*>(sm + Sm::oBar);
+  uint64_t* bar_mma = bar_full + 1;
+  uint64_t* bar_big = bar_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_full + 3);
+  const int n = P.n;
+  const TIo* A = reinterpret_cast<const TIo*>(P.A);
+  TIo* Q = reinterpret_cast<TIo*>(P.Q);
+  const bool use_tma = P.use_tma != 0;
+
+  if ((smem_u32(sm) & 1023u) != 0) __trap();   // the swizzled operand needs 1024-byte aligned atoms
+  if (warp == 0) tmem_alloc<256>(tmem_slot);
+  if (t == 0) {
+    mbar_init(bar_full, 1);
+    mbar_init(bar_mma, 1);
+    mbar_init(bar_big, 1);
+    fence_mbar_init();
+    if (use_tma) tma_prefetch_desc(&tmapA);
+  }
+  // operand images of R_pre (and C)
+  for (int idx = t; idx < NP * NP; idx += 128) {
+    const int k = idx % NP, c = idx / NP;
+    const float v = P.Rpre[idx];
+    const int pk = k >> 4, pc = c >> 4;
+    if (pc == pk) {
+      Rd[k * 16 + (c & 15)] = (c > k) ? -v : 0.f;
+      if (c == k) rinv[k] = __fdiv_rn(1.f, v);
+    } else if (pc > pk) {
+      const uint32_t o = rblk_off<NP>(pk) + kb::off(k & 15, c - 16 * (pk + 1), 16);
+      tile_store<COR>(RbHi, RbLo, o, v);
+    }
+    if (PASS == 2) {
+      char* CHi = big; char* CLo = big + kb::bytes(NP, NP);
+      tile_store<COR>(CHi, CLo, kb::off(k, c, NP), P.C[idx]);
+    }
+  }
+  fence_async_smem();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tm = *tmem_slot;
+  const uint32_t tmU = tm, tmZh = tm + 64, tmZl = tm + 128, tmD = tm + 192;   // D: Gram (pass 1) or Q (pass 2)
+
+  const int tile_beg = blockIdx.x * P.tiles_per_cta;
+  const int tile_end = min(tile_beg + P.tiles_per_cta, P.tiles);
+  const int ntl = max(tile_end - tile_beg, 0);
+  constexpr uint32_t kTileBytes = 128u * NP * sizeof(TIo);
+  // pass 2 walks its tiles backwards: the rows this CTA read last in pass 1 are the likeliest to be in L2
+  auto tile_of = [&](int i) { return PASS == 1 ? tile_beg + i : tile_end - 1 - i; };
+  if (use_tma && t == 0 && ntl > 0) {
+    mbar_arrive_expect_tx(bar_full, kTileBytes);
+    tma_load_2d(land, &tmapA, bar_full, tile_of(0) * kPcTileRows, 0);
+  }
+  uint32_t ph_full = 0, ph_mma = 0, ph_big = 0;
+  float acc[NP];
+#pragma unroll
+  for (int j = 0; j < NP; ++j) acc[j] = 0.f;
+  bool pending = false, first_flush = true;
+  const int glanes = (COR ? 2 : 1) * NP;
+  double* gp = P.Gpart + (size_t)blockIdx.x * NP * 128 + t;
+  auto drain = [&]() {   // G_tile (lane = operand row: Z_hi columns, then Z_lo columns) -> acc
+    mbar_wait(bar_big, ph_big);
+    ph_big ^= 1;
+    fence_after_sync();
+#pragma unroll
+    for (int c0 = 0; c0 < NP; c0 += 16) {
+      float g[16];
+      tmem_ld16(tmem_addr(tmD, warp, c0), g);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) acc[c0 + i] = __fadd_rn(acc[c0 + i], g[i]);
+    }
+  };
+  auto flush = [&]() {
+    if (t < glanes) {
+#pragma unroll
+      for (int j = 0; j < NP; ++j) {
+        const double prev = first_flush ? 0.0 : gp[(size_t)j * 128];
+        gp[(size_t)j * 128] = prev + (double)acc[j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < NP; ++j) acc[j] = 0.f;
+    first_flush = false;
+  };
+
+  for (int it = 0; it < ntl; ++it) {
+    const int tile = tile_of(it);
+    const long long row = (long long)tile * kPcTileRows + t;
+    const bool valid = row < P.M;
+    float y[NP];
+    if (use_tma) {
+      mbar_wait(bar_full, ph_full);
+      ph_full ^= 1;
+#pragma unroll
+      for (int c = 0; c < NP; ++c) y[c] = io_plain(land + c * 128 + t);
+    } else {
+      const TIo* ap = A + row;
+#pragma unroll
+      for (int c = 0; c < NP; ++c) y[c] = (valid && c < n) ? io_plain(ap + (long long)c * P.lda) : 0.f;
+    }
+    __syncthreads();   // every row of the landing buffer is in registers: the next tile may land
+    if (use_tma && t == 0 && it + 1 < ntl) {
+      mbar_arrive_expect_tx(bar_full, kTileBytes);
+      tma_load_2d(land, &tmapA, bar_full, tile_of(it + 1) * kPcTileRows, 0);
+    }
+    if (PASS == 1 && pending) {   // the previous tile's Gram product: its operands and its accumulator are free after this
+      drain();
+      pending = false;
+      if ((it & 15) == 0) flush();
+    }
+#pragma unroll
+    for (int p = 0; p < NPAN; ++p) {
+      if (p > 0) {   // y_p -= sum_{q<p} Z_q R[q, p]
+        mbar_wait(bar_mma, ph_mma);
+        ph_mma ^= 1;
+        fence_after_sync();
+        float u[16];
+        tmem_ld16(tmem_addr(tmU, warp, 16 * p), u);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) y[16 * p + i] = __fsub_rn(y[16 * p + i], u[i]);
+      }
+      // z_p R_pp = y_p : forward substitution along the row, R_pp broadcast from shared memory (stored negated)
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float z = __fmul_rn(y[16 * p + i], rinv[16 * p + i]);
+        y[16 * p + i] = z;
+        const float4* rr = reinterpret_cast<const float4*>(Rd + (16 * p + i) * 16);
+#pragma unroll
+        for (int j4 = (i + 1) / 4; j4 < 4; ++j4) {
+          const float4 q = rr[j4];
+          const float qv[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj)
+            if (4 * j4 + jj > i) y[16 * p + 4 * j4 + jj] = __fmaf_rn(z, qv[jj], y[16 * p + 4 * j4 + jj]);
+        }
+      }
+      if (p < NPAN - 1 || PASS == 2) {   // Z_p -> tensor memory as the A operand of the products that follow
+        float zh[16], zl[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) { zh[i] = COR ? to_tf32_rna(y[16 * p + i]) : y[16 * p + i]; zl[i] = __fsub_rn(y[16 * p + i], zh[i]); }
+        tmem_st16(tmem_addr(tmZh, warp, 16 * p), zh);
+        if (COR) tmem_st16(tmem_addr(tmZl, warp, 16 * p), zl);
+        tmem_wait_st();
+      }
+      if (p < NPAN - 1) {
+        fence_before_sync();
+        __syncthreads();
+        if (t == 0) {
+          fence_after_sync();
+          const int N = NP - 16 * (p + 1);
+          const uint32_t id = idesc_tf32(128, N, false, false, false);
+          const uint32_t bh = smem_u32(RbHi) + rblk_off<NP>(p), bl = smem_u32(RbLo) + rblk_off<NP>(p);
+          const uint32_t d = tmU + 16 * (p + 1);
+#pragma unroll
+          for (int kk = 0; kk < 2; ++kk) {
+            const uint64_t dh = smem_desc(bh + kk * 256, 128, 512), dl = smem_desc(bl + kk * 256, 128, 512);
+            mma_tf32_ts(d, tmZh + 16 * p + 8 * kk, dh, id, p > 0 || kk > 0);
+            if (COR) {
+              mma_tf32_ts(d, tmZh + 16 * p + 8 * kk, dl, id, true);
+              mma_tf32_ts(d, tmZl + 16 * p + 8 * kk, dh, id, true);
+            }
+          }
+          mma_commit(bar_mma);
+        }
+      }
+      if (PASS == 1) {   // Gram operand: column 16p+i of Z at operand line 16p+i (hi) and NP+16p+i (lo)
+        const uint32_t rowpart = (uint32_t)(t >> 5) * sw::kBlock + (uint32_t)((t & 3) << 2);
+        const uint32_t q = (uint32_t)((t & 31) >> 2);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int c = 16 * p + i;
+          const float z = y[c];
+          const float h = to_tf32_rna(z);
+          *reinterpret_cast<float*>(big + rowpart + (uint32_t)c * 128u + ((q ^ (uint32_t)(c & 7)) << 4)) = h;
+          if (COR) *reinterpret_cast<float*>(big + rowpart + (uint32_t)(NP + c) * 128u + ((q ^ (uint32_t)(c & 7)) << 4)) = __fsub_rn(z, h);
+        }
+      }
+    }
+    if (PASS == 1) {
+      fence_async_smem();
+      fence_before_sync();
+      __syncthreads();
+      if (t == 0) {
+        fence_after_sync();
+        sw::gram_issue(tmD, smem_u32(big), NP, 128);
+        mma_commit(bar_big);
+      }
+      pending = true;
+    } else {
+      fence_before_sync();
+      __syncthreads();
+      if (t == 0) {
+        fence_after_sync();
+        const uint32_t id = idesc_tf32(128, NP, false, false, false);
+        const uint32_t ch = smem_u32(big), cl = ch + kb::bytes(NP, NP);
+#pragma unroll
+        for (int kk = 0; kk < NP / 8; ++kk) {
+          const uint64_t dh = smem_desc(ch + kk * 256, 128, kb::sbo(NP)), dl = smem_desc(cl + kk * 256, 128, kb::sbo(NP));
+          mma_tf32_ts(tmD, tmZh + 8 * kk, dh, id, kk > 0);
+          if (COR) {
+            mma_tf32_ts(tmD, tmZh + 8 * kk, dl, id, true);
+            mma_tf32_ts(tmD, tmZl + 8 * kk, dh, id, true);
+          }
+        }
+        mma_commit(bar_big);
+      }
+      mbar_wait(bar_big, ph_big);
+      ph_big ^= 1;
+      fence_after_sync();
+      TIo* qp = Q + row;
+      const bool full = (n == NP) && ((long long)(tile + 1) * kPcTileRows <= P.M);
+#pragma unroll
+      for (int c0 = 0; c0 < NP; c0 += 16) {
+        float qv[16];
+        tmem_ld16(tmem_addr(tmD, warp, c0), qv);
+        if (full) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) io_store(qp + (long long)(c0 + i) * P.ldq, qv[i]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (valid && c0 + i < n) io_store(qp + (long long)(c0 + i) * P.ldq, qv[i]);
+        }
+      }
+    }
+  }
+  if (PASS == 1) {
+    if (pending) drain();
+    flush();   // CTAs without tiles write zeros: the finish kernel sums every slot
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<256>(tm);
+}
+
+// ======================================================================================= finish
+// grid of kFinCtas CTAs x 256 threads: element-wise fp64 sum of the CTA partials in CTA order; the CTA that
+// finishes last (ticket) factors G. Everything after the sum is one CTA of fp64 work on 64 x 64 matrices.
+constexpr int kFinThreads = 256;
+template <int NP>
+__global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __restrict__ Gpart, int nparts, double* __restrict__ Gsum,
+                                                               const float* __restrict__ Rpre, int n, int cor, float max_est,
+                                                               float* __restrict__ Rout, float* __restrict__ Cmat,
+                                                               float* __restrict__ Rzinv, int* __restrict__ status) {
+  extern __shared__ __align__(16) char smraw[];
+  double* G = reinterpret_cast<double*>(smraw);         // [NP][NP] row-major, becomes R_z (upper)
+  double* X = G + NP * NP;                               // R_z^-1 (upper)
+  double* W = X + NP * NP;                               // scratch: G copy for the norm, then G^-1
+  __shared__ double red[kFinThreads / 32];
+  __shared__ int s_last, s_bad;
+  const int t = threadIdx.x;
+  const int lanes = (cor ? 2 : 1) * NP;
+  {
+    const int e = blockIdx.x * kFinThreads + t;         // element (lane l, column j) of the partials
+    if (e < lanes * NP) {
+      const int l = e / NP, j = e % NP;
+      double s = 0.0;
+      const double* p = Gpart + (size_t)j * 128 + l;
+      for (int c = 0; c < nparts; ++c) s += p[(size_t)c * NP * 128];
+      Gsum[e] = s;
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (t == 0) s_last = (atomicAdd(&status[1], 1) == (int)gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (t == 0) s_bad = 0;
+  // G = HH + LH + LH^T, symmetrised; padded columns get a unit diagonal
+  for (int e = t; e < NP * NP; e += kFinThreads) {
+    const int i = e / NP, j = e % NP;
+    double g = 0.5 * (__ldcg(Gsum + i * NP + j) + __ldcg(Gsum + j * NP + i));
+    if (cor) g += __ldcg(Gsum + (NP + i) * NP + j) + __ldcg(Gsum + (NP + j) * NP + i);
+    if (i == j && i >= n) g = 1.0;
+    if (i != j && (i >= n || j >= n)) g = 0.0;
+    G[e] = g;
+    W[e] = g;
+  }
+  __syncthreads();
+  auto block_sumsq = [&](const double* M) {   // over the true n x n block (the padding is a unit diagonal)
+    double s = 0.0;
+    for (int e = t; e < NP * NP; e += kFinThreads)
+      if (e / NP < n && e % NP < n) s += M[e] * M[e];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(kFull, s, o);
+    __syncthreads();
+    if ((t & 31) == 0) red[t >> 5] = s;
+    __syncthreads();
+    double r = 0.0;
+    for (int w = 0; w < kFinThreads / 32; ++w) r += red[w];
+    return r;
+  };
+  const double nG = sqrt(block_sumsq(W));
+  // right-looking Cholesky G = R_z^T R_z, R_z upper, in place (row k of R_z overwrites row k of G)
+  for (int k = 0; k < NP; ++k) {
+    const double d2 = G[k * NP + k];
+    if (!(d2 > 0.0) && t == 0) s_bad = 1;
+    const double d = (d2 > 0.0) ? sqrt(d2) : 1.0;
+    __syncthreads();
+    for (int j = k + t; j < NP; j += kFinThreads) G[k * NP + j] = (j == k) ? d : G[k * NP + j] / d;
+    __syncthreads();
+    const int w = NP - 1 - k;
+    for (int e = t; e < w * w; e += kFinThreads) {
+      const int i = k + 1 + e / w, j = k + 1 + e % w;
+      if (j >= i) G[i * NP + j] -= G[k * NP + i] * G[k * NP + j];
+    }
+    __syncthreads();
+  }
+  // X = R_z^-1 (upper): column c by back substitution, one thread per column
+  if (t < NP) {
+    const int c = t;
+    for (int k = NP - 1; k >= 0; --k) {
+      double s = (k == c) ? 1.0 : 0.0;
+      if (k <= c) {
+        for (int j = k + 1; j <= c; ++j) s -= G[k * NP + j] * X[j * NP + c];
+        s /= G[k * NP + k];
+      } else {
+        s = 0.0;
+      }
+      X[k * NP + c] = s;
+    }
+  }
+  __syncthreads();
+  // G^-1 = X X^T for the certificate
+  for (int e = t; e < NP * NP; e += kFinThreads) {
+    const int i = e / NP, j = e % NP;
+    double s = 0.0;
+    for (int k = max(i, j); k < NP; ++k) s += X[i * NP + k] * X[j * NP + k];
+    W[e] = s;
+  }
+  __syncthreads();
+  const double nGi = sqrt(block_sumsq(W));
+  const double est = nG * nGi / (double)n;
+  // R = R_z R_pre (n x n, ld n), C = R_z^-1
+  for (int e = t; e < NP * NP; e += kFinThreads) {
+    const int i = e % NP, j = e / NP;   // element (i, j) of the column-major outputs
+    double s = 0.0;
+    if (i <= j)
+      for (int k = i; k <= j; ++k) s += G[i * NP + k] * (double)Rpre[k + j * NP];
+    if (i < n && j < n) Rout[i + j * n] = (float)s;
+    const float x = (float)X[i * NP + j];
+    Cmat[i + j * NP] = x;
+    Rzinv[i + j * NP] = x;
+  }
+  __syncthreads();
+  if (t == 0) {
+    const bool ok = !s_bad && (est <= (double)max_est);   // a NaN est compares false
+    status[0] = ok ? kPcOk : 1;
+    status[1] = 0;
+    status[2] = __float_as_int((float)est);
+  }
+}
+
+// C = R_z^-1 B for the row-sharded driver (B = this slab's block of the root factor)
+template <int NP>
+__global__ void __launch_bounds__(256) pc_makec_kernel(const float* __restrict__ Rzinv, const float* __restrict__ B, long long ldb,
+                                                      int n, float* __restrict__ Cmat, const int* __restrict__ status) {
+  if (*status != kPcOk) return;
+  for (int e = threadIdx.x; e < NP * NP; e += 256) {
+    const int i = e % NP, j = e / NP;
+    float s = 0.f;
+    if (i < n && j < n) {
+      for (int k = i; k < n; ++k) s = __fmaf_rn(Rzinv[i + k * NP], B[k + (long long)j * ldb], s);
+    } else if (i == j) {
+      s = 1.f;
+    }
+    Cmat[i + j * NP] = s;
+  }
+}
+
+// ======================================================================================= host side
+using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                              const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                              CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeFn encode_fn() {
+  static EncodeFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess || qres != cudaDriverEntryPointSuccess) {
+      (void)cudaGetLastError();
+      p = nullptr;
+    }
+    return reinterpret_cast<EncodeFn>(p);
+  }();
+  return fn;
+}
+// 2-D map of a column-major M x n matrix: dimension 0 = rows (contiguous), dimension 1 = columns (stride lda);
+// box = 128 rows x NP columns, out-of-range rows and columns read as zero
+bool make_tile_map(CUtensorMap* map, const void* A, long long lda, long long M, int n, int np, IoType io) {
+  EncodeFn fn = encode_fn();
+  const size_t es = io == IoType::f16 ? 2 : 4;
+  if (!fn) return false;
+  if ((reinterpret_cast<uintptr_t>(A) & 15u) != 0 || ((size_t)lda * es) % 16 != 0) return false;
+  if (M >= (1ll << 31)) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)M, (cuuint64_t)n};
+  cuuint64_t gstr[1] = {(cuuint64_t)lda * es};
+  cuuint32_t box[2] = {128u, (cuuint32_t)np};
+  cuuint32_t estr[2] = {1u, 1u};
+  const CUresult r = fn(map, io == IoType::f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                        const_cast<void*>(A), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+template <typename K>
+void set_smem(K kern, int bytes) {
+  TSQR_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+}
+
+template <int NP, bool COR, typename TIo, int PASS>
+void launch_pass_t(const PcParams& p, const CUtensorMap& map, int grid, cudaStream_t s) {
+  auto kern = pc_pass_kernel<NP, COR, TIo, PASS>;
+  static std::once_flag once;
+  std::call_once(once, [&] { set_smem(kern, (int)PassSmem<NP, PASS>::kBytes); });
+  kern<<<grid, 128, PassSmem<NP, PASS>::kBytes, s>>>(p, map);
+  note_launch();
+  TSQR_CUDA_CHECK(cudaGetLastError());
+}
+template <int NP, int PASS>
+void launch_pass_np(const PcParams& p, const CUtensorMap& map, int grid, bool cor, IoType io, cudaStream_t s) {
+  if (io == IoType::f16) launch_pass_t<NP, false, __half, PASS>(p, map, grid, s);
+  else if (cor) launch_pass_t<NP, true, float, PASS>(p, map, grid, s);
+  else launch_pass_t<NP, false, float, PASS>(p, map, grid, s);
+}
+template <int PASS>
+void launch_pass(int np, const PcParams& p, const CUtensorMap& map, int grid, bool cor, IoType io, cudaStream_t s) {
+  switch (np) {
+    case 16: launch_pass_np<16, PASS>(p, map, grid, cor, io, s); break;
+    case 32: launch_pass_np<32, PASS>(p, map, grid, cor, io, s); break;
+    default: launch_pass_np<64, PASS>(p, map, grid, cor, io, s); break;
+  }
+}
+
+template <int NP, typename TIo>
+void launch_sample_t(const PcCall& c, cudaStream_t s) {
+  auto kern = pc_sample_kernel<NP, TIo>;
+  static std::once_flag once;
+  std::call_once(once, [&] { set_smem(kern, (int)SmpCfg<NP>::kBytes); });
+  kern<<<1, 8 * NP, SmpCfg<NP>::kBytes, s>>>(reinterpret_cast<const TIo*>(c.A), c.lda, c.M, c.n, c.ws + c.L.rpre,
+                                              reinterpret_cast<int*>(c.ws + c.L.status));
+  note_launch();
+  TSQR_CUDA_CHECK(cudaGetLastError());
+}
+template <int NP>
+void launch_finish_t(const PcCall& c, cudaStream_t s) {
+  auto kern = pc_finish_kernel<NP>;
+  const int bytes = 3 * NP * NP * (int)sizeof(double);
+  static std::once_flag once;
+  std::call_once(once, [&] { set_smem(kern, bytes); });
+  const int lanes = (c.cor ? 2 : 1) * NP;
+  const int grid = (lanes * NP + kFinThreads - 1) / kFinThreads;
+  kern<<<grid, kFinThreads, bytes, s>>>(reinterpret_cast<const double*>(c.ws + c.L.gpart), c.L.grid,
+                                         reinterpret_cast<double*>(c.ws + c.L.gsum), c.ws + c.L.rpre, c.n, c.cor ? 1 : 0,
+                                         kPcMaxEst, c.ws + c.L.rout, c.ws + c.L.cmat, c.ws + c.L.rzinv,
+                                         reinterpret_cast<int*>(c.ws + c.L.status));
+  note_launch();
+  TSQR_CUDA_CHECK(cudaGetLastError());
+}
+
+PcParams pass_params(const PcCall& c) {
+  PcParams p{};
+  p.A = c.A; p.lda = c.lda; p.M = c.M; p.n = c.n;
+  p.Q = c.Q; p.ldq = c.ldq;
+  p.Rpre = c.ws + c.L.rpre;
+  p.C = c.ws + c.L.cmat;
+  p.Gpart = reinterpret_cast<double*>(c.ws + c.L.gpart);
+  p.status = reinterpret_cast<int*>(c.ws + c.L.status);
+  p.tiles = (int)c.L.tiles;
+  p.tiles_per_cta = c.L.tiles_per_cta;
+  return p;
+}
+
+size_t align64(size_t x) { return (x + 63) / 64 * 64; }
+// TSQR_B200_TMA=0 makes the passes load their tiles with per-thread global loads (the path taken anyway when
+// lda * sizeof(element) is not a multiple of 16 bytes)
+bool tma_enabled() {
+  static const bool on = [] { const char* e = std::getenv("TSQR_B200_TMA"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
+}  // namespace
+
+PcLayout pc_layout(long long m, int n) {
+  PcLayout L;
+  L.np = tc_np(n);
+  L.tiles = (m + kPcTileRows - 1) / kPcTileRows;
+  const long long want = 2ll * device_sm_count();
+  L.grid = (int)std::min<long long>(want, L.tiles);
+  L.tiles_per_cta = (int)((L.tiles + L.grid - 1) / L.grid);
+  L.grid = (int)((L.tiles + L.tiles_per_cta - 1) / L.tiles_per_cta);
+  const size_t np2 = (size_t)L.np * L.np;
+  size_t off = 0;
+  L.rpre = off; off = align64(off + np2);
+  L.status = off; off = align64(off + 16);
+  L.rout = off; off = align64(off + np2);
+  L.cmat = off; off = align64(off + np2);
+  L.rzinv = off; off = align64(off + np2);
+  L.gsum = off; off = align64(off + 2 * (2 * np2));                       // doubles
+  // sized for the largest grid any device of this process can ask for (the query may run before a device is chosen)
+  const size_t gmax = (size_t)std::max<long long>(L.grid, std::min<long long>(2 * 160, L.tiles));
+  L.gpart = off; off = align64(off + 2 * gmax * (size_t)L.np * 128);      // doubles
+  L.total = off;
+  return L;
+}
+
+void pc_reduce(const PcCall& c, cudaStream_t s) {
+  const int np = c.L.np;
+  {
+    ProfScope prof(s, 100);
+    if (c.io == IoType::f16) {
+      switch (np) { case 16: launch_sample_t<16, __half>(c, s); break; case 32: launch_sample_t<32, __half>(c, s); break; default: launch_sample_t<64, __half>(c, s); }
+    } else {
+      switch (np) { case 16: launch_sample_t<16, float>(c, s); break; case 32: launch_sample_t<32, float>(c, s); break; default: launch_sample_t<64, float>(c, s); }
+    }
+  }
+  PcParams p = pass_params(c);
+  CUtensorMap map;
+  memset(&map, 0, sizeof(map));
+  p.use_tma = (tma_enabled() && make_tile_map(&map, c.A, c.lda, c.M, c.n, np, c.io)) ? 1 : 0;
+  {
+    ProfScope prof(s, 101);
+    launch_pass<1>(np, p, map, c.L.grid, c.cor, c.io, s);
+  }
+  {
+    ProfScope prof(s, 102);
+    switch (np) { case 16: launch_finish_t<16>(c, s); break; case 32: launch_finish_t<32>(c, s); break; default: launch_finish_t<64>(c, s); }
+  }
+}
+
+namespace {
+__global__ void pc_set_status_kernel(int* status, int v) { status[0] = v; }
+}  // namespace
+
+// pass 1 with a caller-supplied R_pre, then pass 2 with a caller-supplied C (tests of the operand layouts)
+void pc_probe(const PcCall& c, const float* rpre, const float* cmat, double* gsum_out, bool use_tma, cudaStream_t s) {
+  const int np = c.L.np;
+  const size_t np2 = (size_t)np * np;
+  int* status = reinterpret_cast<int*>(c.ws + c.L.status);
+  TSQR_CUDA_CHECK(cudaMemsetAsync(status, 0, 16 * sizeof(int), s));
+  TSQR_CUDA_CHECK(cudaMemcpyAsync(c.ws + c.L.rpre, rpre, np2 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  PcParams p = pass_params(c);
+  CUtensorMap map;
+  memset(&map, 0, sizeof(map));
+  p.use_tma = (use_tma && make_tile_map(&map, c.A, c.lda, c.M, c.n, np, c.io)) ? 1 : 0;
+  if (use_tma && !p.use_tma) throw std::runtime_error("tsqr_b200: no TMA map for this matrix (alignment)");
+  launch_pass<1>(np, p, map, c.L.grid, c.cor, c.io, s);
+  switch (np) { case 16: launch_finish_t<16>(c, s); break; case 32: launch_finish_t<32>(c, s); break; default: launch_finish_t<64>(c, s); }
+  TSQR_CUDA_CHECK(cudaMemcpyAsync(gsum_out, c.ws + c.L.gsum, 2 * np2 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  TSQR_CUDA_CHECK(cudaMemcpyAsync(c.ws + c.L.cmat, cmat, np2 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  pc_set_status_kernel<<<1, 1, 0, s>>>(status, kPcOk);
+  launch_pass<2>(np, p, map, c.L.grid, c.cor, c.io, s);
+}
+
+void pc_build(const PcCall& c, const float* B, long long ldb, cudaStream_t s) {
+  const int np = c.L.np;
+  if (B) {
+    const int* st = reinterpret_cast<const int*>(c.ws + c.L.status);
+    switch (np) {
+      case 16: pc_makec_kernel<16><<<1, 256, 0, s>>>(c.ws + c.L.rzinv, B, ldb, c.n, c.ws + c.L.cmat, st); break;
+      case 32: pc_makec_kernel<32><<<1, 256, 0, s>>>(c.ws + c.L.rzinv, B, ldb, c.n, c.ws + c.L.cmat, st); break;
+      default: pc_makec_kernel<64><<<1, 256, 0, s>>>(c.ws + c.L.rzinv, B, ldb, c.n, c.ws + c.L.cmat, st); break;
+    }
+    note_launch();
+    TSQR_CUDA_CHECK(cudaGetLastError());
+  }
+  PcParams p = pass_params(c);
+  CUtensorMap map;
+  memset(&map, 0, sizeof(map));
+  p.use_tma = (tma_enabled() && make_tile_map(&map, c.A, c.lda, c.M, c.n, np, c.io)) ? 1 : 0;
+  launch_pass<2>(np, p, map, c.L.grid, c.cor, c.io, s);
+}
+
+}  // namespace tsqr_b200

@@ -77,15 +77,18 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+// Bounded spin: a wait that never completes (a lost arrive, a wrong transaction count) traps the kernel
+// after ~2^26 probes instead of hanging the device.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   const uint32_t addr = smem_u32(bar);
-  uint32_t ok;
+  uint32_t ok, spins = 0;
   do {
     asm volatile(
         "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
         : "=r"(ok)
         : "r"(addr), "r"(parity)
         : "memory");
+    if (!ok && ++spins > (1u << 26)) __trap();
   } while (!ok);
 }
 // all previously issued tcgen05.mma of this thread arrive on `bar` when they complete
@@ -104,6 +107,83 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+
+// D[tmem] (+)= A[tmem] * B[smem]: the A operand (M = 128 lanes x K = 8 consecutive 32-bit columns) is read
+// straight from tensor memory, where the threads put it with tcgen05.st (row r of the tile = lane r)
+__device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, bool accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"((uint32_t)accumulate)
+      : "memory");
+}
+
+// ---- TMA (cp.async.bulk.tensor): one elected thread arms the mbarrier with the byte count of the box and
+// issues the copy; the box lands in shared memory and completes the transaction on the barrier
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+// box origin (c0 = index along the contiguous dimension, c1 = index along the strided one)
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const void* tmap, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// the shared-memory source of every committed store group has been read (the buffer may be rewritten)
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// =========================================================================================
+// "sw" tile buffer: K-major operand with the 128-byte hardware swizzle (layout_type 2), K = tile rows.
+// One K block = 32 rows (128 bytes of a column); inside a K block, operand row m (= matrix column) is a
+// 128-byte line whose 16-byte chunks are XOR-swizzled with m % 8; 8 lines form a 1024-byte atom
+// (SBO = 1024). A K block holds kLines operand rows, so hi (lines [0, NP)) and lo (lines [NP, 2 NP))
+// parts of one tile are ONE M = 128 operand. Thread-per-row stores of one column hit 32 distinct banks.
+namespace sw {
+constexpr uint32_t kLines = 128;                       // operand rows per K block
+constexpr uint32_t kBlock = kLines * 128;              // 16384 bytes per K block
+__host__ __device__ constexpr uint32_t bytes(int rows) { return (uint32_t)(rows / 32) * kBlock; }
+__device__ __forceinline__ uint32_t off(int row, int line) {
+  return (uint32_t)(row >> 5) * kBlock + (uint32_t)line * 128u + (uint32_t)((((row & 31) >> 2) ^ (line & 7)) << 4) +
+         (uint32_t)((row & 3) << 2);
+}
+// D[128 x N] = sum over rows [0, krows) of OP[m][row] * OP[n][row], m < 128 lines, n < N lines
+__device__ __forceinline__ void gram_issue(uint32_t d_tmem, uint32_t base, int N, int krows) {
+  const uint32_t id = idesc_tf32(128, N, false, false, false);
+  bool acc = false;
+  for (int kb = 0; kb < krows / 32; ++kb) {
+    const uint64_t d0 = smem_desc(base + (uint32_t)kb * kBlock, 16, 1024, 2);
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+      const uint64_t d = d0 + (uint64_t)(kk * 2);   // +32 bytes in the 16-byte units of the address field
+      mma_tf32(d_tmem, d, d, id, acc);
+      acc = true;
+    }
+  }
+}
+}  // namespace sw
+
+// small K-major no-swizzle B operand blocks with dense (128-byte) core matrices, written once per kernel:
+// element (k, c) of a K x N block: (c/8)*SBO + (k/4)*128 + (c%8)*16 + (k%4)*4, SBO = (K/4)*128
+namespace kb {
+__host__ __device__ constexpr uint32_t sbo(int K) { return (uint32_t)(K / 4) * 128u; }
+__host__ __device__ constexpr uint32_t bytes(int K, int N) { return (uint32_t)(N / 8) * sbo(K); }
+__device__ __forceinline__ uint32_t off(int k, int c, int K) {
+  return (uint32_t)(c >> 3) * sbo(K) + (uint32_t)(k >> 2) * 128u + (uint32_t)((c & 7) << 4) + (uint32_t)((k & 3) << 2);
+}
+}  // namespace kb
 
 // ---- TMEM allocation (one full warp calls alloc / dealloc)
 template <int COLS>

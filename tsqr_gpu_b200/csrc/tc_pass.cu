@@ -133,6 +133,7 @@ __device__ __forceinline__ void sweep16(float* Pbuf, const float* Rd, float* Rn,
 template <int NP, bool COR, typename TIn, typename TQ>
 __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
   extern __shared__ __align__(128) char sm[];
+  if (P.skip_ok && *P.skip_ok == kPcOk) return;
   float* Rd = reinterpret_cast<float*>(sm + rMisc);
   float* Rn = Rd + 272;
   float* Sp = Rn + 272;
@@ -172,7 +173,7 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
     for (int idx = t; idx < NP * NP; idx += kT) {
       const int r = idx % NP, c = idx / NP;
       const long long row = cbeg + r;
-      Hs[c * LD + r] = (row < cend && c < n) ? io_load(A + row + (long long)c * P.lda) : 0.f;
+      Hs[c * LD + r] = (row < cend && c < n) ? io_plain(A + row + (long long)c * P.lda) : 0.f;
     }
     __syncthreads();
     for (int j = 0; j < NP; ++j) {
@@ -225,7 +226,7 @@ __global__ void __launch_bounds__(kT, 2) tc_reduce_kernel(const TcParams P) {
     for (int c0 = 0; c0 < NP; c0 += 16) {
       float a[16];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) a[i] = (valid && c0 + i < n) ? io_load(A + row + (long long)(c0 + i) * P.lda) : 0.f;
+      for (int i = 0; i < 16; ++i) a[i] = (valid && c0 + i < n) ? io_plain(A + row + (long long)(c0 + i) * P.lda) : 0.f;
       if (c0 == 0) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) Pbuf[i * kPS + t] = a[i];

@@ -80,7 +80,9 @@ struct TcParams {
   long long lds;
   const float* Bsrc;         // build: parent Q, chunk c uses rows [c*n, c*n+n); nullptr => identity
   long long ldb;
+  const int* skip_ok;        // when set: the kernel returns at once if *skip_ok == kPcOk (the PC path did the work)
 };
+constexpr int kPcOk = 0x600D;    // status word of the preconditioned-Cholesky path: certificate passed
 constexpr int kTcTileRows = 128;
 inline int tc_np(int n) { return n <= 16 ? 16 : (n <= 32 ? 32 : 64); }
 void launch_tc_reduce(const TcParams& p, bool corrected, IoType in, IoType q, cudaStream_t s);
