@@ -117,8 +117,8 @@ def test_certificate_rejects_and_householder_takes_over(cuda, oracle, case):
         a[:, 20] = a[:, 3]
     st, est, orth, res, _ = _run(oracle, a, "fp32_tc_cor")
     print(f"{case}: status {st} est {est} orth {orth:.2e} res {res:.2e}")
-    if case != "graded_rows":        # graded rows may or may not pass the certificate; either way the result must hold
-        assert st == 0, "the certificate must reject this input"
+    if case in ("zero_head", "zero_column"):   # the other two may or may not pass the certificate (a duplicated column
+        assert st == 0, "the certificate must reject this input"   # leaves a rounding-level pivot: a valid QR either way)
     assert res < 5e-6
     if case != "rank_deficient":     # Q of a rank-deficient matrix is still orthogonal with Householder reflectors
         assert orth < 5e-6

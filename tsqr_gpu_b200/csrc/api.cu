@@ -152,11 +152,14 @@ int tsqr_b200_pc_status(int mode, size_t m, size_t n, const void* ws, void* stre
   if (!use_pc(mode, (long long)m)) return -1;
   return guarded([&] {
     Plan plan = make_plan_for(mode, (long long)m, (int)n);
-    int st[4] = {0, 0, 0, 0};
+    int st[16] = {0};
     TSQR_CUDA_CHECK(cudaMemcpyAsync(st, (const float*)ws + plan.pc_off + plan.pcl.status, sizeof(st), cudaMemcpyDeviceToHost,
                                     (cudaStream_t)stream));
     TSQR_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
     if (est) std::memcpy(est, &st[2], sizeof(float));
+    if (std::getenv("TSQR_B200_PC_PHASES"))   // SM-clock cycles of the single-CTA phases (tuning aid)
+      std::fprintf(stderr, "tsqr_b200 pc phases: sample gather %d sweep %d | finish chol %d inverse %d rest %d\n", st[8], st[9],
+                   st[4], st[5], st[6]);
     return st[0] == kPcOk ? 1 : 0;
   });
 }

@@ -61,32 +61,28 @@ __device__ __forceinline__ HhScal hh_scalars(float alpha, float g) {
   h.tau = ok ? __fmaf_rn(fabsf(alpha), rcp_approx(norm), 1.f) : 2.f;
   return h;
 }
-template <int NW>
-__device__ __forceinline__ float part_sum(const float* p) {
-  float s0 = 0.f, s1 = 0.f;
-#pragma unroll
-  for (int i = 0; i < NW; i += 4) {
-    const float4 v = *reinterpret_cast<const float4*>(p + i);
-    s0 = __fadd_rn(s0, __fadd_rn(v.x, v.y));
-    s1 = __fadd_rn(s1, __fadd_rn(v.z, v.w));
-  }
-  return __fadd_rn(s0, s1);
-}
-
 template <int NP>
 struct SmpCfg {
   static constexpr int H = 8 * NP, T = 8 * NP, NW = T / 32, PS = H + 4, LD = NP + 1, KP = NP / 16;
+  static constexpr int PLD = NP + 4;     // row stride of the per-warp partials: stage-2 reads are at most 2-way conflicted
+  static constexpr int GW = NW < 8 ? NW : 8;   // threads that share one column in stage 2, each sums NW / GW partials
   static constexpr uint32_t oTile = 0;
   static constexpr uint32_t oR = oTile + NP * PS * 4;
-  static constexpr uint32_t oPart = oR + NP * LD * 4;
-  static constexpr uint32_t kBytes = oPart + 2 * NP * NW * 4 + 16;
+  static constexpr uint32_t oPart = oR + NP * LD * 4;            // [NW][PLD] partials
+  static constexpr uint32_t oTot = oPart + NW * PLD * 4;         // 2 x [NP] column totals (double buffered)
+  static constexpr uint32_t kBytes = oTot + 2 * NP * 4 + 16;
 };
 
+// One Householder step needs, for every live column c, g_c = x_j . a_c over all H rows. Each warp owns 32 rows:
+// stage 1 = per-thread partial (16 rows) + one shuffle, written as part[warp][c] (consecutive lanes, consecutive
+// words); stage 2 = thread (c = t / 8, g = t % 8) adds NW / 8 of the warp partials of column c, three shuffles
+// finish the sum, tot[c] is published for everybody. Two block barriers per step, no bank conflict worth the name.
 template <int PJ, int NP>
-__device__ __forceinline__ void smp_sweep_panel(f32x2 (&a)[NP / 16][8], float* tileS, float* Rs, float* part, int t) {
+__device__ __forceinline__ void smp_sweep_panel(f32x2 (&a)[NP / 16][8], float* tileS, float* Rs, float* part, float* tot, int t) {
   using Cf = SmpCfg<NP>;
-  constexpr int KP = Cf::KP, NW = Cf::NW, PS = Cf::PS, LD = Cf::LD, K0 = PJ;
+  constexpr int KP = Cf::KP, NW = Cf::NW, PS = Cf::PS, LD = Cf::LD, PLD = Cf::PLD, GW = Cf::GW, K0 = PJ;
   const int cl = t & 15, s = t >> 4, lane = t & 31, warp = t >> 5;
+  const int c2 = t / GW, g2 = t % GW;
 #pragma unroll 1
   for (int jl = 0; jl < 16; ++jl) {
     const int j = 16 * PJ + jl;
@@ -101,7 +97,6 @@ __device__ __forceinline__ void smp_sweep_panel(f32x2 (&a)[NP / 16][8], float* t
     float rjc[KP];
 #pragma unroll
     for (int k = K0; k < KP; ++k) rjc[k] = Rs[j * LD + cl + 16 * k];
-    float* pb = part + (jl & 1) * (NP * NW);
 #pragma unroll
     for (int k = K0; k < KP; ++k) {
       f32x2 q0 = 0ull, q1 = 0ull;
@@ -112,14 +107,26 @@ __device__ __forceinline__ void smp_sweep_panel(f32x2 (&a)[NP / 16][8], float* t
       unpack2(q1, p2, p3);
       float p = __fadd_rn(__fadd_rn(p0, p1), __fadd_rn(p2, p3));
       p = __fadd_rn(p, __shfl_xor_sync(kFull, p, 16));
-      if (lane < 16) pb[(cl + 16 * k) * NW + warp] = p;
+      if (lane < 16) part[warp * PLD + cl + 16 * k] = p;
     }
     __syncthreads();
-    const HhScal h = hh_scalars(alpha, part_sum<NW>(pb + j * NW));
+    float* tb = tot + (jl & 1) * NP;
+    {
+      float q = 0.f;
+      if (c2 < NP && c2 >= 16 * K0) {
+#pragma unroll
+        for (int w = 0; w < NW / GW; ++w) q = __fadd_rn(q, part[(g2 * (NW / GW) + w) * PLD + c2]);
+      }
+#pragma unroll
+      for (int o = GW / 2; o > 0; o >>= 1) q = __fadd_rn(q, __shfl_xor_sync(kFull, q, o));
+      if (g2 == 0 && c2 < NP) tb[c2] = q;
+    }
+    __syncthreads();
+    const HhScal h = hh_scalars(alpha, tb[j]);
 #pragma unroll
     for (int k = K0; k < KP; ++k) {
       const int c = cl + 16 * k;
-      const float g = part_sum<NW>(pb + c * NW);
+      const float g = tb[c];
       const float coef = __fmul_rn(h.tau, __fmaf_rn(g, h.rden, rjc[k]));
       const bool active = (k > K0) || (cl > jl);
       const float ncv = active ? -__fmul_rn(coef, h.rden) : 0.f;
@@ -146,14 +153,14 @@ __device__ __forceinline__ void smp_sweep_panel(f32x2 (&a)[NP / 16][8], float* t
 }
 template <int PJ, int NP>
 struct SmpSweepAll {
-  static __device__ __forceinline__ void run(f32x2 (&a)[NP / 16][8], float* tileS, float* Rs, float* part, int t) {
-    smp_sweep_panel<PJ, NP>(a, tileS, Rs, part, t);
-    SmpSweepAll<PJ + 1, NP>::run(a, tileS, Rs, part, t);
+  static __device__ __forceinline__ void run(f32x2 (&a)[NP / 16][8], float* tileS, float* Rs, float* part, float* tot, int t) {
+    smp_sweep_panel<PJ, NP>(a, tileS, Rs, part, tot, t);
+    SmpSweepAll<PJ + 1, NP>::run(a, tileS, Rs, part, tot, t);
   }
 };
 template <int NP>
 struct SmpSweepAll<NP / 16, NP> {
-  static __device__ __forceinline__ void run(f32x2 (&)[NP / 16][8], float*, float*, float*, int) {}
+  static __device__ __forceinline__ void run(f32x2 (&)[NP / 16][8], float*, float*, float*, float*, int) {}
 };
 
 template <int NP, typename TIo>
@@ -165,7 +172,9 @@ __global__ void __launch_bounds__(8 * NP, 1) pc_sample_kernel(const TIo* __restr
   float* tileS = reinterpret_cast<float*>(sm + Cf::oTile);
   float* Rs = reinterpret_cast<float*>(sm + Cf::oR);
   float* part = reinterpret_cast<float*>(sm + Cf::oPart);
+  float* tot = reinterpret_cast<float*>(sm + Cf::oTot);
   const int t = threadIdx.x, cl = t & 15, s = t >> 4;
+  const long long clk0 = clock64();
   if (t == 0) { status[0] = 0; status[1] = 0; }
   {
     const long long row = ((long long)t * M) / H;   // sample row t of H, evenly spread over the matrix
@@ -175,6 +184,7 @@ __global__ void __launch_bounds__(8 * NP, 1) pc_sample_kernel(const TIo* __restr
   }
   for (int i = t; i < NP * LD; i += T) Rs[i] = 0.f;
   __syncthreads();
+  const long long clk1 = clock64();
   f32x2 a[KP][8];
 #pragma unroll
   for (int k = 0; k < KP; ++k) {
@@ -182,8 +192,9 @@ __global__ void __launch_bounds__(8 * NP, 1) pc_sample_kernel(const TIo* __restr
 #pragma unroll
     for (int i = 0; i < 4; ++i) { const ulonglong2 v = src[i]; a[k][2 * i] = v.x; a[k][2 * i + 1] = v.y; }
   }
-  SmpSweepAll<0, NP>::run(a, tileS, Rs, part, t);
+  SmpSweepAll<0, NP>::run(a, tileS, Rs, part, tot, t);
   __syncthreads();
+  if (t == 0) { status[8] = (int)(clk1 - clk0); status[9] = (int)(clock64() - clk1); }   // phase clocks (cycles): gather, sweep
   for (int i = t; i < NP * NP; i += T) {
     const int k = i % NP, c = i / NP;
     float v = 0.f;
@@ -231,7 +242,8 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
   uint64_t* bar_full = reinterpret_cast<uint64_t*>(sm + Sm::oBar);
   uint64_t* bar_mma = bar_full + 1;
   uint64_t* bar_big = bar_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_full + 3);
+  uint64_t* bar_empty = bar_full + 3;   // 128 arrivals: every row of the landing buffer has been read
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_full + 4);
   const int n = P.n;
   const TIo* A = reinterpret_cast<const TIo*>(P.A);
   TIo* Q = reinterpret_cast<TIo*>(P.Q);
@@ -243,6 +255,7 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
     mbar_init(bar_full, 1);
     mbar_init(bar_mma, 1);
     mbar_init(bar_big, 1);
+    mbar_init(bar_empty, 128);
     fence_mbar_init();
     if (use_tma) tma_prefetch_desc(&tmapA);
   }
@@ -280,7 +293,7 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
     mbar_arrive_expect_tx(bar_full, kTileBytes);
     tma_load_2d(land, &tmapA, bar_full, tile_of(0) * kPcTileRows, 0);
   }
-  uint32_t ph_full = 0, ph_mma = 0, ph_big = 0;
+  uint32_t ph_full = 0, ph_mma = 0, ph_big = 0, ph_empty = 0;
   float acc[NP];
 #pragma unroll
   for (int j = 0; j < NP; ++j) acc[j] = 0.f;
@@ -322,15 +335,22 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
       ph_full ^= 1;
 #pragma unroll
       for (int c = 0; c < NP; ++c) y[c] = io_plain(land + c * 128 + t);
+      // Release the landing buffer. Measured on B200: neither bar.sync nor mbarrier.arrive waits for shared-memory
+      // loads that have been issued but whose data has not come back, and the next TMA (async proxy) write into
+      // the buffer overtakes them (the last columns of a tile read the next tile, once in ~30000 tiles). The
+      // cross-proxy fence (MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC in SASS) completes the loads before the release.
+      fence_async_smem();
+      mbar_arrive(bar_empty);
+      if (t == 0 && it + 1 < ntl) {
+        mbar_wait(bar_empty, ph_empty);
+        mbar_arrive_expect_tx(bar_full, kTileBytes);
+        tma_load_2d(land, &tmapA, bar_full, tile_of(it + 1) * kPcTileRows, 0);
+      }
+      ph_empty ^= 1;
     } else {
       const TIo* ap = A + row;
 #pragma unroll
       for (int c = 0; c < NP; ++c) y[c] = (valid && c < n) ? io_plain(ap + (long long)c * P.lda) : 0.f;
-    }
-    __syncthreads();   // every row of the landing buffer is in registers: the next tile may land
-    if (use_tma && t == 0 && it + 1 < ntl) {
-      mbar_arrive_expect_tx(bar_full, kTileBytes);
-      tma_load_2d(land, &tmapA, bar_full, tile_of(it + 1) * kPcTileRows, 0);
     }
     if (PASS == 1 && pending) {   // the previous tile's Gram product: its operands and its accumulator are free after this
       drain();
@@ -463,30 +483,49 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
 }
 
 // ======================================================================================= finish
-// grid of kFinCtas CTAs x 256 threads: element-wise fp64 sum of the CTA partials in CTA order; the CTA that
-// finishes last (ticket) factors G. Everything after the sum is one CTA of fp64 work on 64 x 64 matrices.
+// Stage 1, every CTA: fp64 sum of the per-CTA partials for 32 consecutive accumulator lanes of one Gram column
+// (warp w adds partials w, w + 8, ...: coalesced 256-byte reads, then the 8 warp sums are added in fixed order).
+// Stage 2, the CTA that finishes last (ticket): chol(G), certificate, R = R_z R_pre, C = R_z^-1, all in fp64 on
+// 64 x 64 matrices in shared memory.
 constexpr int kFinThreads = 256;
+__device__ __forceinline__ double rcp_f64(double x) {   // 1/x to fp64 accuracy from the fp32 approximation (x > 0, normal)
+  double y = (double)rcp_approx((float)x);
+  y = fma(y, fma(-x, y, 1.0), y);
+  y = fma(y, fma(-x, y, 1.0), y);
+  y = fma(y, fma(-x, y, 1.0), y);
+  return y;
+}
 template <int NP>
 __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __restrict__ Gpart, int nparts, double* __restrict__ Gsum,
                                                                const float* __restrict__ Rpre, int n, int cor, float max_est,
                                                                float* __restrict__ Rout, float* __restrict__ Cmat,
                                                                float* __restrict__ Rzinv, int* __restrict__ status) {
   extern __shared__ __align__(16) char smraw[];
-  double* G = reinterpret_cast<double*>(smraw);         // [NP][NP] row-major, becomes R_z (upper)
-  double* X = G + NP * NP;                               // R_z^-1 (upper)
-  double* W = X + NP * NP;                               // scratch: G copy for the norm, then G^-1
-  __shared__ double red[kFinThreads / 32];
+  double* G = reinterpret_cast<double*>(smraw);         // [NP][NP] row-major: trailing matrix of the factorisation, then G^-1
+  double* Rz = G + NP * NP;                              // R_z (upper)
+  double* X = Rz + NP * NP;                              // R_z^-1 (upper)
+  __shared__ double red[kFinThreads / 32][32];
+  __shared__ double rdiag[NP];
   __shared__ int s_last, s_bad;
-  const int t = threadIdx.x;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int lanes = (cor ? 2 : 1) * NP;
   {
-    const int e = blockIdx.x * kFinThreads + t;         // element (lane l, column j) of the partials
-    if (e < lanes * NP) {
-      const int l = e / NP, j = e % NP;
-      double s = 0.0;
-      const double* p = Gpart + (size_t)j * 128 + l;
-      for (int c = 0; c < nparts; ++c) s += p[(size_t)c * NP * 128];
-      Gsum[e] = s;
+    const int nlb = (lanes + 31) / 32;
+    const int lb = blockIdx.x % nlb, j = blockIdx.x / nlb;
+    const int l = 32 * lb + lane;
+    double s = 0.0;
+    const double* p = Gpart + (size_t)j * 128 + l;
+    if (l < lanes) {
+#pragma unroll 4
+      for (int c = warp; c < nparts; c += kFinThreads / 32) s += __ldcg(p + (size_t)c * NP * 128);
+    }
+    red[warp][lane] = s;
+    __syncthreads();
+    if (warp == 0 && l < lanes) {
+      double r = 0.0;
+#pragma unroll
+      for (int w = 0; w < kFinThreads / 32; ++w) r += red[w][lane];
+      Gsum[l * NP + j] = r;
     }
   }
   __threadfence();
@@ -495,8 +534,10 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
   __syncthreads();
   if (!s_last) return;
   __threadfence();
+  const long long fclk0 = clock64();
   if (t == 0) s_bad = 0;
   // G = HH + LH + LH^T, symmetrised; padded columns get a unit diagonal
+  double ssq = 0.0;
   for (int e = t; e < NP * NP; e += kFinThreads) {
     const int i = e / NP, j = e % NP;
     double g = 0.5 * (__ldcg(Gsum + i * NP + j) + __ldcg(Gsum + j * NP + i));
@@ -504,69 +545,73 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
     if (i == j && i >= n) g = 1.0;
     if (i != j && (i >= n || j >= n)) g = 0.0;
     G[e] = g;
-    W[e] = g;
+    if (i < n && j < n) ssq += g * g;
   }
-  __syncthreads();
-  auto block_sumsq = [&](const double* M) {   // over the true n x n block (the padding is a unit diagonal)
-    double s = 0.0;
-    for (int e = t; e < NP * NP; e += kFinThreads)
-      if (e / NP < n && e % NP < n) s += M[e] * M[e];
+  auto block_sum = [&](double v) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(kFull, s, o);
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
     __syncthreads();
-    if ((t & 31) == 0) red[t >> 5] = s;
+    if (lane == 0) red[0][warp] = v;
     __syncthreads();
     double r = 0.0;
-    for (int w = 0; w < kFinThreads / 32; ++w) r += red[w];
+    for (int w = 0; w < kFinThreads / 32; ++w) r += red[0][w];
     return r;
   };
-  const double nG = sqrt(block_sumsq(W));
-  // right-looking Cholesky G = R_z^T R_z, R_z upper, in place (row k of R_z overwrites row k of G)
+  const double nG = sqrt(block_sum(ssq));
+  // right-looking Cholesky G = R_z^T R_z with ONE barrier per step: row k of R_z goes to its own array, the
+  // trailing update uses the unscaled row k of G and 1 / G_kk
   for (int k = 0; k < NP; ++k) {
-    const double d2 = G[k * NP + k];
-    if (!(d2 > 0.0) && t == 0) s_bad = 1;
-    const double d = (d2 > 0.0) ? sqrt(d2) : 1.0;
-    __syncthreads();
-    for (int j = k + t; j < NP; j += kFinThreads) G[k * NP + j] = (j == k) ? d : G[k * NP + j] / d;
-    __syncthreads();
+    const double piv = G[k * NP + k];
+    const bool okp = piv > 0.0 && piv < 1e300;
+    if (!okp && t == 0) s_bad = 1;
+    const double inv = okp ? rcp_f64(piv) : 1.0;
+    if (t < NP - k) {
+      const double rs = sqrt(inv);                     // 1 / sqrt(G_kk)
+      Rz[k * NP + k + t] = G[k * NP + k + t] * rs;
+      if (t == 0) rdiag[k] = rs;                       // 1 / R_z[k][k]
+    }
+    if (t >= NP - k && t < NP) Rz[k * NP + (t - (NP - k))] = 0.0;   // below the diagonal
     const int w = NP - 1 - k;
     for (int e = t; e < w * w; e += kFinThreads) {
       const int i = k + 1 + e / w, j = k + 1 + e % w;
-      if (j >= i) G[i * NP + j] -= G[k * NP + i] * G[k * NP + j];
+      if (j >= i) G[i * NP + j] -= G[k * NP + i] * G[k * NP + j] * inv;
     }
     __syncthreads();
   }
-  // X = R_z^-1 (upper): column c by back substitution, one thread per column
-  if (t < NP) {
-    const int c = t;
+  const long long fclk1 = clock64();
+  // X = R_z^-1 (upper): column c by back substitution, 4 adjacent lanes share a column and split the dot products
+  {
+    const int c = t >> 2, g4 = t & 3;
     for (int k = NP - 1; k >= 0; --k) {
-      double s = (k == c) ? 1.0 : 0.0;
-      if (k <= c) {
-        for (int j = k + 1; j <= c; ++j) s -= G[k * NP + j] * X[j * NP + c];
-        s /= G[k * NP + k];
-      } else {
-        s = 0.0;
-      }
-      X[k * NP + c] = s;
+      double s = 0.0;
+      if (k < c && c < NP)
+        for (int j = k + 1 + g4; j <= c; j += 4) s -= Rz[k * NP + j] * X[j * NP + c];
+      s += __shfl_xor_sync(kFull, s, 1);
+      s += __shfl_xor_sync(kFull, s, 2);
+      if (g4 == 0 && c < NP) X[k * NP + c] = (k > c) ? 0.0 : ((k == c ? 1.0 : 0.0) + s) * rdiag[k];
+      __syncwarp();
     }
   }
   __syncthreads();
-  // G^-1 = X X^T for the certificate
+  const long long fclk2 = clock64();
+  // G^-1 = X X^T for the certificate (into the dead trailing-matrix array)
+  double ssi = 0.0;
   for (int e = t; e < NP * NP; e += kFinThreads) {
     const int i = e / NP, j = e % NP;
-    double s = 0.0;
-    for (int k = max(i, j); k < NP; ++k) s += X[i * NP + k] * X[j * NP + k];
-    W[e] = s;
+    double s0 = 0.0, s1 = 0.0;
+    int k = max(i, j);
+    for (; k + 1 < NP; k += 2) { s0 += X[i * NP + k] * X[j * NP + k]; s1 += X[i * NP + k + 1] * X[j * NP + k + 1]; }
+    if (k < NP) s0 += X[i * NP + k] * X[j * NP + k];
+    if (i < n && j < n) ssi += (s0 + s1) * (s0 + s1);
   }
-  __syncthreads();
-  const double nGi = sqrt(block_sumsq(W));
+  const double nGi = sqrt(block_sum(ssi));
   const double est = nG * nGi / (double)n;
   // R = R_z R_pre (n x n, ld n), C = R_z^-1
   for (int e = t; e < NP * NP; e += kFinThreads) {
     const int i = e % NP, j = e / NP;   // element (i, j) of the column-major outputs
     double s = 0.0;
     if (i <= j)
-      for (int k = i; k <= j; ++k) s += G[i * NP + k] * (double)Rpre[k + j * NP];
+      for (int k = i; k <= j; ++k) s += Rz[i * NP + k] * (double)Rpre[k + j * NP];
     if (i < n && j < n) Rout[i + j * n] = (float)s;
     const float x = (float)X[i * NP + j];
     Cmat[i + j * NP] = x;
@@ -578,6 +623,9 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
     status[0] = ok ? kPcOk : 1;
     status[1] = 0;
     status[2] = __float_as_int((float)est);
+    status[4] = (int)(fclk1 - fclk0);          // phase clocks (cycles): G build + Cholesky, inverse, the rest
+    status[5] = (int)(fclk2 - fclk1);
+    status[6] = (int)(clock64() - fclk2);
   }
 }
 
@@ -678,7 +726,7 @@ void launch_finish_t(const PcCall& c, cudaStream_t s) {
   static std::once_flag once;
   std::call_once(once, [&] { set_smem(kern, bytes); });
   const int lanes = (c.cor ? 2 : 1) * NP;
-  const int grid = (lanes * NP + kFinThreads - 1) / kFinThreads;
+  const int grid = ((lanes + 31) / 32) * NP;
   kern<<<grid, kFinThreads, bytes, s>>>(reinterpret_cast<const double*>(c.ws + c.L.gpart), c.L.grid,
                                          reinterpret_cast<double*>(c.ws + c.L.gsum), c.ws + c.L.rpre, c.n, c.cor ? 1 : 0,
                                          kPcMaxEst, c.ws + c.L.rout, c.ws + c.L.cmat, c.ws + c.L.rzinv,
