@@ -3,7 +3,7 @@
 numpy restatement of the preconditioned-Cholesky TSQR that tsqr_gpu_b200/csrc/pc_tsqr.cu runs for the *_tc_*
 modes (the executable specification of that path, like oracle/ts_flat.py is for the Householder passes):
 
-    sample : h = 8 NP rows of A at stride M / h          -> R_pre (Householder QR of the sample)
+    sample : h = 8 NP rows of A (h/16 clusters of 16 rows) -> R_pre (Householder QR of the sample)
     pass 1 : Z = A R_pre^-1 (substitution), G = Z^T Z      (per 128-row tile, fp32; partial sums in fp64)
     finish : R_z = chol(G); est = |G|_F |G^-1|_F / n; R = R_z R_pre; C = R_z^-1
     pass 2 : Q = Z C
@@ -23,8 +23,11 @@ def padded(n):
 
 
 def sample_rows(m, n):
+    """h = 8 NP rows: h / 16 clusters of 16 consecutive rows spread evenly over the matrix (pc_sample_kernel)"""
     h = 8 * padded(n)
-    return (np.arange(h, dtype=np.int64) * m) // h
+    ncl = h // 16
+    t = np.arange(h, dtype=np.int64)
+    return ((t // 16) * (m - 16)) // max(ncl - 1, 1) + (t % 16)
 
 
 def pc_tsqr(a, work=np.float32, tile=128):

@@ -39,6 +39,35 @@ struct PcParams {
   int tiles, tiles_per_cta, use_tma;
 };
 
+// Image of R_pre's diagonal blocks for the forward substitution, in CONSTANT memory: [k][16] = -R[k][16 (k/16) + j]
+// (zero up to the diagonal), then 1 / R[k][k] at kImgInv + k. Every thread of a tile uses the same values: as
+// constant-bank operands of the FFMAs they cost no load instruction and no L1TEX bandwidth (as 160 broadcast
+// LDS.128 per thread and tile they kept the shared-memory pipe 70 % busy and bounded both passes). The image is
+// written per call by a stream-ordered device-to-device copy; kImgSlots slots, guarded by events, keep calls on
+// different streams apart; the kernels are instantiated per slot so that the operands are immediate addresses.
+constexpr int kImgInv = 64 * 16;
+constexpr int kImgFloats = kImgInv + 64;
+constexpr int kImgSlots = 3;
+__constant__ float c_img0[kImgFloats];
+__constant__ float c_img1[kImgFloats];
+__constant__ float c_img2[kImgFloats];
+template <int SLOT>
+__device__ __forceinline__ const float* cimg() {
+  if constexpr (SLOT == 0) return c_img0;
+  else if constexpr (SLOT == 1) return c_img1;
+  else return c_img2;
+}
+// global staging copy of the image (source of the cudaMemcpyToSymbolAsync)
+__device__ __forceinline__ void cimg_store(float* img, int NP, int k, int c, float v) {
+  if ((k >> 4) == (c >> 4)) {
+    img[k * 16 + (c & 15)] = (c > k) ? -v : 0.f;
+    if (c == k) img[kImgInv + k] = __fdiv_rn(1.f, v);
+  }
+}
+__global__ void pc_cimg_kernel(const float* __restrict__ Rpre, float* __restrict__ img, int NP) {
+  for (int idx = threadIdx.x; idx < NP * NP; idx += blockDim.x) cimg_store(img, NP, idx % NP, idx / NP, Rpre[idx]);
+}
+
 __device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float rsqrt_approx(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
@@ -165,10 +194,11 @@ struct SmpSweepAll<NP / 16, NP> {
 
 template <int NP, typename TIo>
 __global__ void __launch_bounds__(8 * NP, 1) pc_sample_kernel(const TIo* __restrict__ A, long long lda, long long M, int n,
-                                                             float* __restrict__ Rpre, int* __restrict__ status) {
+                                                             float* __restrict__ Rpre, float* __restrict__ img,
+                                                             int* __restrict__ status) {
   using Cf = SmpCfg<NP>;
   constexpr int H = Cf::H, T = Cf::T, PS = Cf::PS, LD = Cf::LD, KP = Cf::KP;
-  extern __shared__ __align__(128) char sm[];
+  extern __shared__ __align__(1024) char sm[];
   float* tileS = reinterpret_cast<float*>(sm + Cf::oTile);
   float* Rs = reinterpret_cast<float*>(sm + Cf::oR);
   float* part = reinterpret_cast<float*>(sm + Cf::oPart);
@@ -177,10 +207,16 @@ __global__ void __launch_bounds__(8 * NP, 1) pc_sample_kernel(const TIo* __restr
   const long long clk0 = clock64();
   if (t == 0) { status[0] = 0; status[1] = 0; }
   {
-    const long long row = ((long long)t * M) / H;   // sample row t of H, evenly spread over the matrix
+    // sample row t = row (t % 16) of cluster t / 16; the H / 16 clusters of 16 consecutive rows (one 64-byte piece
+    // per column) are spread evenly over the matrix. All NP loads of a thread are issued before the first store.
+    const long long cl0 = (((long long)(t >> 4) * (M - 16)) / (H / 16 - 1 > 0 ? H / 16 - 1 : 1));
+    const long long row = cl0 + (t & 15);
     const TIo* ap = A + row;
-#pragma unroll 8
-    for (int c = 0; c < NP; ++c) tileS[c * PS + t] = (c < n) ? io_load(ap + (long long)c * lda) : 0.f;
+    float v[NP];
+#pragma unroll
+    for (int c = 0; c < NP; ++c) v[c] = (c < n) ? io_load(ap + (long long)c * lda) : 0.f;
+#pragma unroll
+    for (int c = 0; c < NP; ++c) tileS[c * PS + t] = v[c];
   }
   for (int i = t; i < NP * LD; i += T) Rs[i] = 0.f;
   __syncthreads();
@@ -201,6 +237,7 @@ __global__ void __launch_bounds__(8 * NP, 1) pc_sample_kernel(const TIo* __restr
     if (k < n && c < n) v = (k <= c) ? Rs[k * LD + c] : 0.f;
     else if (k == c) v = 1.f;
     Rpre[k + c * NP] = v;
+    cimg_store(img, NP, k, c, v);
   }
 }
 
@@ -220,13 +257,11 @@ struct PassSmem {
   static constexpr uint32_t kRblk = rblk_off<NP>(NPAN - 1);
   static constexpr uint32_t oRblkHi = oBig + kBig;
   static constexpr uint32_t oRblkLo = oRblkHi + kRblk;
-  static constexpr uint32_t oRd = oRblkLo + kRblk;                                      // -R diagonal blocks, [NP][16]
-  static constexpr uint32_t oRinv = oRd + NP * 16 * 4;
-  static constexpr uint32_t oBar = oRinv + NP * 4;                                      // 3 mbarriers, tmem slot
+  static constexpr uint32_t oBar = oRblkLo + kRblk;                                     // 4 mbarriers, tmem slot
   static constexpr uint32_t kBytes = oBar + 64;
 };
 
-template <int NP, bool COR, typename TIo, int PASS>
+template <int NP, bool COR, typename TIo, int PASS, int SLOT>
 __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const __grid_constant__ CUtensorMap tmapA) {
   using Sm = PassSmem<NP, PASS>;
   constexpr int NPAN = NP / 16;
@@ -237,8 +272,7 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
   char* big = sm + Sm::oBig;
   char* RbHi = sm + Sm::oRblkHi;
   char* RbLo = sm + Sm::oRblkLo;
-  float* Rd = reinterpret_cast<float*>(sm + Sm::oRd);
-  float* rinv = reinterpret_cast<float*>(sm + Sm::oRinv);
+  const float* ci = cimg<SLOT>();
   uint64_t* bar_full = reinterpret_cast<uint64_t*>(sm + Sm::oBar);
   uint64_t* bar_mma = bar_full + 1;
   uint64_t* bar_big = bar_full + 2;
@@ -264,10 +298,7 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
     const int k = idx % NP, c = idx / NP;
     const float v = P.Rpre[idx];
     const int pk = k >> 4, pc = c >> 4;
-    if (pc == pk) {
-      Rd[k * 16 + (c & 15)] = (c > k) ? -v : 0.f;
-      if (c == k) rinv[k] = __fdiv_rn(1.f, v);
-    } else if (pc > pk) {
+    if (pc > pk) {
       const uint32_t o = rblk_off<NP>(pk) + kb::off(k & 15, c - 16 * (pk + 1), 16);
       tile_store<COR>(RbHi, RbLo, o, v);
     }
@@ -368,20 +399,13 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
 #pragma unroll
         for (int i = 0; i < 16; ++i) y[16 * p + i] = __fsub_rn(y[16 * p + i], u[i]);
       }
-      // z_p R_pp = y_p : forward substitution along the row, R_pp broadcast from shared memory (stored negated)
+      // z_p R_pp = y_p : forward substitution along the row, -R_pp and 1 / diag as constant-bank operands
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
-        const float z = __fmul_rn(y[16 * p + i], rinv[16 * p + i]);
+        const float z = __fmul_rn(y[16 * p + i], ci[kImgInv + 16 * p + i]);
         y[16 * p + i] = z;
-        const float4* rr = reinterpret_cast<const float4*>(Rd + (16 * p + i) * 16);
 #pragma unroll
-        for (int j4 = (i + 1) / 4; j4 < 4; ++j4) {
-          const float4 q = rr[j4];
-          const float qv[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-          for (int jj = 0; jj < 4; ++jj)
-            if (4 * j4 + jj > i) y[16 * p + 4 * j4 + jj] = __fmaf_rn(z, qv[jj], y[16 * p + 4 * j4 + jj]);
-        }
+        for (int j = i + 1; j < 16; ++j) y[16 * p + j] = __fmaf_rn(z, ci[(16 * p + i) * 16 + j], y[16 * p + j]);
       }
       if (p < NPAN - 1 || PASS == 2) {   // Z_p -> tensor memory as the A operand of the products that follow
         float zh[16], zl[16];
@@ -482,6 +506,208 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
   if (warp == 0) tmem_dealloc<256>(tm);
 }
 
+// ======================================================================================= pass 2, v2
+// Q = (A R_pre^-1) C with FOUR tiles in flight per SM: one CTA of 4 warp groups per SM, each warp group an
+// independent 128-row tile pipeline. What makes four fit where pc_pass_kernel<2> holds two:
+//   * the Z_p operand of the tcgen05 products is staged in shared memory (row-wise "rn" layout, 16 KB per warp
+//     group, reused panel after panel), so a tile needs 112 TMEM columns (U: 48, Q accumulator: 64), not 256;
+//   * the tile lands panel by panel (TMA boxes of 128 x 16 into a ring of kApSlots slots per warp group) and is
+//     consumed panel by panel: 16 values per thread live instead of 64, ~100 registers;
+//   * Q accumulates panel by panel: D += Z_p C[16p : 16p+16, :] is issued together with the substitution update
+//     U += Z_p R[p, trail], so nothing of Z outlives its panel.
+// A landing slot is handed back after the panel's Z stores -- every loaded value has been consumed by then, which
+// is the ordering the TMA (async proxy) write needs (see the note in pc_pass_kernel).
+constexpr int kApSlots = 3;
+constexpr int kApWg = 4;
+template <int NP, typename TIo>
+struct ApplySmem {
+  static constexpr int NPAN = NP / 16;
+  static constexpr uint32_t kC = 2 * kb::bytes(NP, NP);
+  static constexpr uint32_t kRblk = rblk_off<NP>(NPAN - 1);
+  static constexpr uint32_t oC = 0;
+  static constexpr uint32_t oRblkHi = oC + kC;
+  static constexpr uint32_t oRblkLo = oRblkHi + kRblk;
+  static constexpr uint32_t oBar = oRblkLo + kRblk;                      // per warp group: full[S], empty[S], mma; then the tmem slot
+  static constexpr uint32_t kBarBytes = 256;
+  static constexpr uint32_t kSlot = 128u * 16u * sizeof(TIo);           // one landed panel
+  static constexpr uint32_t kZop = rn::bytes(16);                        // 8192: one 128 x 16 operand (hi or lo)
+  static constexpr uint32_t kWg = kApSlots * kSlot + 2 * kZop;
+  static constexpr uint32_t oWg = (oBar + kBarBytes + 1023) / 1024 * 1024;
+  static constexpr uint32_t kBytes = oWg + kApWg * kWg;
+};
+
+template <int NP, bool COR, typename TIo, int SLOT>
+__global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams P, const __grid_constant__ CUtensorMap tmapP) {
+  using Sm = ApplySmem<NP, TIo>;
+  constexpr int NPAN = NP / 16, S = kApSlots;
+  extern __shared__ __align__(1024) char sm[];
+  if (*P.status != kPcOk) return;   // the Householder passes behind this launch do the work
+  const int tid = threadIdx.x, wg = tid >> 7, t = tid & 127, warp = (tid >> 5) & 3;
+  char* CHi = sm + Sm::oC;
+  char* CLo = CHi + kb::bytes(NP, NP);
+  char* RbHi = sm + Sm::oRblkHi;
+  char* RbLo = sm + Sm::oRblkLo;
+  const float* ci = cimg<SLOT>();
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + Sm::oBar) + wg * (2 * S + 1);
+  uint64_t* bar_full = bars;
+  uint64_t* bar_empty = bars + S;
+  uint64_t* bar_mma = bars + 2 * S;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + Sm::oBar + Sm::kBarBytes - 8);
+  char* wgbase = sm + Sm::oWg + wg * Sm::kWg;
+  char* ZHi = wgbase + S * Sm::kSlot;
+  char* ZLo = ZHi + Sm::kZop;
+  const int n = P.n;
+  const TIo* A = reinterpret_cast<const TIo*>(P.A);
+  TIo* Q = reinterpret_cast<TIo*>(P.Q);
+  const bool use_tma = P.use_tma != 0;
+
+  if (tid < 32) tmem_alloc<512>(tmem_slot);
+  if (t == 0) {
+    for (int i = 0; i < S; ++i) { mbar_init(bar_full + i, 1); mbar_init(bar_empty + i, 128); }
+    mbar_init(bar_mma, 1);
+    fence_mbar_init();
+    if (use_tma && wg == 0) tma_prefetch_desc(&tmapP);
+  }
+  for (int idx = tid; idx < NP * NP; idx += 128 * kApWg) {   // operand images of R_pre and C
+    const int k = idx % NP, c = idx / NP;
+    const float v = P.Rpre[idx];
+    const int pk = k >> 4, pc = c >> 4;
+    if (pc > pk) tile_store<COR>(RbHi, RbLo, rblk_off<NP>(pk) + kb::off(k & 15, c - 16 * (pk + 1), 16), v);
+    tile_store<COR>(CHi, CLo, kb::off(k, c, NP), P.C[idx]);
+  }
+  fence_async_smem();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tm = *tmem_slot + 128u * wg;
+  const uint32_t tmU = tm, tmD = tm + 64;   // U column of tile column c (>= 16): tmU + c - 16
+
+  // this warp group's tiles: every kApWg-th tile of the CTA's range, walked backwards (see pc_pass_kernel)
+  const int tile_beg = blockIdx.x * P.tiles_per_cta;
+  const int tile_end = min(tile_beg + P.tiles_per_cta, P.tiles);
+  const int ntl_cta = max(tile_end - tile_beg, 0);
+  const int ntl = ntl_cta > wg ? (ntl_cta - wg + kApWg - 1) / kApWg : 0;
+  auto tile_of = [&](int i) { return tile_end - 1 - (wg + kApWg * i); };
+  const int npanels = ntl * NPAN;
+  auto issue_load = [&](int g) {   // panel g of this warp group's stream -> slot g % S
+    const int slot = g % S;
+    mbar_arrive_expect_tx(bar_full + slot, Sm::kSlot);
+    tma_load_2d(wgbase + slot * Sm::kSlot, &tmapP, bar_full + slot, tile_of(g / NPAN) * kPcTileRows, 16 * (g % NPAN));
+  };
+  if (use_tma && t == 0)
+    for (int g = 0; g < S && g < npanels; ++g) issue_load(g);
+  uint32_t ph_mma = 0;
+
+  for (int it = 0; it < ntl; ++it) {
+    const int tile = tile_of(it);
+    const long long row = (long long)tile * kPcTileRows + t;
+    const bool valid = row < P.M;
+#pragma unroll
+    for (int p = 0; p < NPAN; ++p) {
+      const int g = it * NPAN + p, slot = g % S;
+      float y[16];
+      if (use_tma) {
+        mbar_wait(bar_full + slot, (uint32_t)(g / S) & 1u);
+        const TIo* land = reinterpret_cast<const TIo*>(wgbase + slot * Sm::kSlot);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) y[i] = io_plain(land + i * 128 + t);
+      } else {
+        const TIo* ap = A + row + (long long)(16 * p) * P.lda;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) y[i] = (valid && 16 * p + i < n) ? io_plain(ap + (long long)i * P.lda) : 0.f;
+      }
+      if (p > 0 || it > 0) {   // the products that read Z_{p-1} (and, for p = 0, the previous tile's) are complete
+        if (p > 0) {
+          mbar_wait(bar_mma, ph_mma);
+          ph_mma ^= 1;
+          fence_after_sync();
+          float u[16];
+          tmem_ld16(tmem_addr(tmU, warp, 16 * (p - 1)), u);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) y[i] = __fsub_rn(y[i], u[i]);
+        }
+      }
+      // z_p R_pp = y_p, -R_pp and 1 / diag as constant-bank operands
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float z = __fmul_rn(y[i], ci[kImgInv + 16 * p + i]);
+        y[i] = z;
+#pragma unroll
+        for (int j = i + 1; j < 16; ++j) y[j] = __fmaf_rn(z, ci[(16 * p + i) * 16 + j], y[j]);
+      }
+#pragma unroll
+      for (int c4 = 0; c4 < 4; ++c4) rn::store4<COR>(ZHi, ZLo, t, c4, y[4 * c4], y[4 * c4 + 1], y[4 * c4 + 2], y[4 * c4 + 3]);
+      fence_async_smem();
+      if (use_tma) {   // every value of the slot has been consumed (the stores above depend on all of them)
+        mbar_arrive(bar_empty + slot);
+        if (t == 0 && g + S < npanels) {
+          mbar_wait(bar_empty + slot, (uint32_t)(g / S) & 1u);
+          issue_load(g + S);
+        }
+      }
+      fence_before_sync();
+      named_bar_sync(1 + wg, 128);
+      if (t == 0) {
+        fence_after_sync();
+        const uint32_t zh = smem_u32(ZHi), zl = smem_u32(ZLo);
+        if (p < NPAN - 1) {   // U[:, 16(p+1):] (+)= Z_p R[p, 16(p+1):]
+          const int N = NP - 16 * (p + 1);
+          const uint32_t id = idesc_tf32(128, N, false, false, false);
+          const uint32_t bh = smem_u32(RbHi) + rblk_off<NP>(p), bl = smem_u32(RbLo) + rblk_off<NP>(p);
+          const uint32_t d = tmU + 16 * p;
+#pragma unroll
+          for (int kk = 0; kk < 2; ++kk) {
+            const uint64_t ah = smem_desc(zh + kk * 4096, 2048, 128), al = smem_desc(zl + kk * 4096, 2048, 128);
+            const uint64_t dh = smem_desc(bh + kk * 256, 128, 512), dl = smem_desc(bl + kk * 256, 128, 512);
+            mma_tf32(d, ah, dh, id, p > 0 || kk > 0);
+            if (COR) {
+              mma_tf32(d, ah, dl, id, true);
+              mma_tf32(d, al, dh, id, true);
+            }
+          }
+        }
+        {   // Q (+)= Z_p C[16p : 16p+16, :]
+          const uint32_t id = idesc_tf32(128, NP, false, false, false);
+          const uint32_t ch = smem_u32(CHi) + p * 512, cl = smem_u32(CLo) + p * 512;
+#pragma unroll
+          for (int kk = 0; kk < 2; ++kk) {
+            const uint64_t ah = smem_desc(zh + kk * 4096, 2048, 128), al = smem_desc(zl + kk * 4096, 2048, 128);
+            const uint64_t dh = smem_desc(ch + kk * 256, 128, kb::sbo(NP)), dl = smem_desc(cl + kk * 256, 128, kb::sbo(NP));
+            mma_tf32(tmD, ah, dh, id, p > 0 || kk > 0);
+            if (COR) {
+              mma_tf32(tmD, ah, dl, id, true);
+              mma_tf32(tmD, al, dh, id, true);
+            }
+          }
+        }
+        mma_commit(bar_mma);
+      }
+    }
+    // Q tile
+    mbar_wait(bar_mma, ph_mma);
+    ph_mma ^= 1;
+    fence_after_sync();
+    TIo* qp = Q + row;
+    const bool full = (n == NP) && ((long long)(tile + 1) * kPcTileRows <= P.M);
+#pragma unroll
+    for (int c0 = 0; c0 < NP; c0 += 16) {
+      float qv[16];
+      tmem_ld16(tmem_addr(tmD, warp, c0), qv);
+      if (full) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) io_store(qp + (long long)(c0 + i) * P.ldq, qv[i]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if (valid && c0 + i < n) io_store(qp + (long long)(c0 + i) * P.ldq, qv[i]);
+      }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (tid < 32) tmem_dealloc<512>(*tmem_slot);
+}
+
 // ======================================================================================= finish
 // Stage 1, every CTA: fp64 sum of the per-CTA partials for 32 consecutive accumulator lanes of one Gram column
 // (warp w adds partials w, w + 8, ...: coalesced 256-byte reads, then the 8 warp sums are added in fixed order).
@@ -559,22 +785,29 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
   };
   const double nG = sqrt(block_sum(ssq));
   // right-looking Cholesky G = R_z^T R_z with ONE barrier per step: row k of R_z goes to its own array, the
-  // trailing update uses the unscaled row k of G and 1 / G_kk
+  // trailing update uses the unscaled row k of G and 1 / G_kk. Thread (warp, lane) owns rows warp + 8a and columns
+  // lane + 32b of the trailing matrix: row k is read with consecutive lanes, G[k][i] is a broadcast.
   for (int k = 0; k < NP; ++k) {
     const double piv = G[k * NP + k];
     const bool okp = piv > 0.0 && piv < 1e300;
     if (!okp && t == 0) s_bad = 1;
     const double inv = okp ? rcp_f64(piv) : 1.0;
-    if (t < NP - k) {
+    if (t < NP) {
       const double rs = sqrt(inv);                     // 1 / sqrt(G_kk)
-      Rz[k * NP + k + t] = G[k * NP + k + t] * rs;
-      if (t == 0) rdiag[k] = rs;                       // 1 / R_z[k][k]
+      Rz[k * NP + t] = (t >= k) ? G[k * NP + t] * rs : 0.0;
+      if (t == k) rdiag[k] = rs;                       // 1 / R_z[k][k]
     }
-    if (t >= NP - k && t < NP) Rz[k * NP + (t - (NP - k))] = 0.0;   // below the diagonal
-    const int w = NP - 1 - k;
-    for (int e = t; e < w * w; e += kFinThreads) {
-      const int i = k + 1 + e / w, j = k + 1 + e % w;
-      if (j >= i) G[i * NP + j] -= G[k * NP + i] * G[k * NP + j] * inv;
+#pragma unroll
+    for (int b2 = 0; b2 < (NP + 31) / 32; ++b2) {
+      const int j = lane + 32 * b2;
+      if (j > k && j < NP) {
+        const double gkj = G[k * NP + j] * inv;
+#pragma unroll
+        for (int a2 = 0; a2 < (NP + 7) / 8; ++a2) {
+          const int i = warp + 8 * a2;
+          if (i > k && i <= j && i < NP) G[i * NP + j] -= G[k * NP + i] * gkj;
+        }
+      }
     }
     __syncthreads();
   }
@@ -594,28 +827,55 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
   }
   __syncthreads();
   const long long fclk2 = clock64();
-  // G^-1 = X X^T for the certificate (into the dead trailing-matrix array)
-  double ssi = 0.0;
+  // XT = X^T and the fp64 image of R_pre go over the dead trailing matrix and one more array, so that every product
+  // below reads one broadcast operand and one operand with consecutive lanes
+  double* XT = G;                                        // XT[k][j] = X[j][k]
+  double* Rp = X + NP * NP;                              // Rp[k][j] = R_pre[k][j]
   for (int e = t; e < NP * NP; e += kFinThreads) {
-    const int i = e / NP, j = e % NP;
-    double s0 = 0.0, s1 = 0.0;
-    int k = max(i, j);
-    for (; k + 1 < NP; k += 2) { s0 += X[i * NP + k] * X[j * NP + k]; s1 += X[i * NP + k + 1] * X[j * NP + k + 1]; }
-    if (k < NP) s0 += X[i * NP + k] * X[j * NP + k];
-    if (i < n && j < n) ssi += (s0 + s1) * (s0 + s1);
+    const int k = e / NP, j = e % NP;
+    XT[e] = X[j * NP + k];
+    Rp[e] = (double)Rpre[k + j * NP];
+  }
+  __syncthreads();
+  // G^-1 = X X^T for the certificate: entry (i, j), i = warp + 8a, j = lane + 32b
+  double ssi = 0.0;
+#pragma unroll 1
+  for (int a2 = 0; a2 < (NP + 7) / 8; ++a2) {
+    const int i = warp + 8 * a2;
+#pragma unroll
+    for (int b2 = 0; b2 < (NP + 31) / 32; ++b2) {
+      const int j = lane + 32 * b2;
+      if (i < n && j < n) {
+        double s0 = 0.0, s1 = 0.0;
+        int k = max(i, j);
+        for (; k + 1 < NP; k += 2) { s0 += X[i * NP + k] * XT[k * NP + j]; s1 += X[i * NP + k + 1] * XT[(k + 1) * NP + j]; }
+        if (k < NP) s0 += X[i * NP + k] * XT[k * NP + j];
+        ssi += (s0 + s1) * (s0 + s1);
+      }
+    }
   }
   const double nGi = sqrt(block_sum(ssi));
   const double est = nG * nGi / (double)n;
   // R = R_z R_pre (n x n, ld n), C = R_z^-1
-  for (int e = t; e < NP * NP; e += kFinThreads) {
-    const int i = e % NP, j = e / NP;   // element (i, j) of the column-major outputs
-    double s = 0.0;
-    if (i <= j)
-      for (int k = i; k <= j; ++k) s += Rz[i * NP + k] * (double)Rpre[k + j * NP];
-    if (i < n && j < n) Rout[i + j * n] = (float)s;
-    const float x = (float)X[i * NP + j];
-    Cmat[i + j * NP] = x;
-    Rzinv[i + j * NP] = x;
+#pragma unroll 1
+  for (int a2 = 0; a2 < (NP + 7) / 8; ++a2) {
+    const int i = warp + 8 * a2;
+#pragma unroll
+    for (int b2 = 0; b2 < (NP + 31) / 32; ++b2) {
+      const int j = lane + 32 * b2;
+      if (i < NP && j < NP) {
+        double s0 = 0.0, s1 = 0.0;
+        if (i <= j) {
+          int k = i;
+          for (; k + 1 <= j; k += 2) { s0 += Rz[i * NP + k] * Rp[k * NP + j]; s1 += Rz[i * NP + k + 1] * Rp[(k + 1) * NP + j]; }
+          if (k <= j) s0 += Rz[i * NP + k] * Rp[k * NP + j];
+        }
+        if (i < n && j < n) Rout[i + j * n] = (float)(s0 + s1);
+        const float x = (float)XT[i * NP + j];             // X[j][i]: element (j, i) of the column-major outputs
+        Cmat[j + i * NP] = x;
+        Rzinv[j + i * NP] = x;
+      }
+    }
   }
   __syncthreads();
   if (t == 0) {
@@ -664,7 +924,7 @@ EncodeFn encode_fn() {
 }
 // 2-D map of a column-major M x n matrix: dimension 0 = rows (contiguous), dimension 1 = columns (stride lda);
 // box = 128 rows x NP columns, out-of-range rows and columns read as zero
-bool make_tile_map(CUtensorMap* map, const void* A, long long lda, long long M, int n, int np, IoType io) {
+bool make_tile_map(CUtensorMap* map, const void* A, long long lda, long long M, int n, int np, IoType io, int box_cols = 0) {
   EncodeFn fn = encode_fn();
   const size_t es = io == IoType::f16 ? 2 : 4;
   if (!fn) return false;
@@ -672,7 +932,7 @@ bool make_tile_map(CUtensorMap* map, const void* A, long long lda, long long M, 
   if (M >= (1ll << 31)) return false;
   cuuint64_t gdim[2] = {(cuuint64_t)M, (cuuint64_t)n};
   cuuint64_t gstr[1] = {(cuuint64_t)lda * es};
-  cuuint32_t box[2] = {128u, (cuuint32_t)np};
+  cuuint32_t box[2] = {128u, (cuuint32_t)(box_cols > 0 ? box_cols : np)};
   cuuint32_t estr[2] = {1u, 1u};
   const CUresult r = fn(map, io == IoType::f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
                         const_cast<void*>(A), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -680,33 +940,115 @@ bool make_tile_map(CUtensorMap* map, const void* A, long long lda, long long M, 
   return r == CUDA_SUCCESS;
 }
 
+// TSQR_B200_TMA=0 makes the passes load their tiles with per-thread global loads (the path taken anyway when
+// lda * sizeof(element) is not a multiple of 16 bytes)
+bool tma_enabled() {
+  static const bool on = [] { const char* e = std::getenv("TSQR_B200_TMA"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 template <typename K>
 void set_smem(K kern, int bytes) {
   TSQR_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
 }
 
-template <int NP, bool COR, typename TIo, int PASS>
-void launch_pass_t(const PcParams& p, const CUtensorMap& map, int grid, cudaStream_t s) {
-  auto kern = pc_pass_kernel<NP, COR, TIo, PASS>;
+// ---- constant-image slots: a slot is (re)written by a stream-ordered copy only after the event of its previous
+// user has completed on the new user's stream
+struct ImgSlots {
+  std::mutex mu;
+  cudaEvent_t ev[64][kImgSlots] = {};
+  unsigned next[64] = {};
+};
+ImgSlots& img_slots() { static ImgSlots s; return s; }
+int img_acquire(const float* img_global, cudaStream_t s) {
+  ImgSlots& st = img_slots();
+  int dev = 0;
+  TSQR_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) dev = 0;
+  int slot;
+  {
+    std::lock_guard<std::mutex> lk(st.mu);
+    slot = (int)(st.next[dev]++ % kImgSlots);
+    if (!st.ev[dev][slot]) TSQR_CUDA_CHECK(cudaEventCreateWithFlags(&st.ev[dev][slot], cudaEventDisableTiming));
+    else TSQR_CUDA_CHECK(cudaStreamWaitEvent(s, st.ev[dev][slot], 0));
+  }
+  const size_t bytes = kImgFloats * sizeof(float);
+  switch (slot) {
+    case 0: TSQR_CUDA_CHECK(cudaMemcpyToSymbolAsync(c_img0, img_global, bytes, 0, cudaMemcpyDeviceToDevice, s)); break;
+    case 1: TSQR_CUDA_CHECK(cudaMemcpyToSymbolAsync(c_img1, img_global, bytes, 0, cudaMemcpyDeviceToDevice, s)); break;
+    default: TSQR_CUDA_CHECK(cudaMemcpyToSymbolAsync(c_img2, img_global, bytes, 0, cudaMemcpyDeviceToDevice, s)); break;
+  }
+  return slot;
+}
+void img_release(int slot, cudaStream_t s) {
+  ImgSlots& st = img_slots();
+  int dev = 0;
+  TSQR_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) dev = 0;
+  std::lock_guard<std::mutex> lk(st.mu);
+  TSQR_CUDA_CHECK(cudaEventRecord(st.ev[dev][slot], s));
+}
+
+template <int NP, bool COR, typename TIo, int SLOT>
+void launch_pass1_t(const PcParams& p, const CUtensorMap& map, int grid, cudaStream_t s) {
+  auto kern = pc_pass_kernel<NP, COR, TIo, 1, SLOT>;
   static std::once_flag once;
-  std::call_once(once, [&] { set_smem(kern, (int)PassSmem<NP, PASS>::kBytes); });
-  kern<<<grid, 128, PassSmem<NP, PASS>::kBytes, s>>>(p, map);
+  std::call_once(once, [&] { set_smem(kern, (int)PassSmem<NP, 1>::kBytes); });
+  kern<<<grid, 128, PassSmem<NP, 1>::kBytes, s>>>(p, map);
   note_launch();
   TSQR_CUDA_CHECK(cudaGetLastError());
 }
-template <int NP, int PASS>
-void launch_pass_np(const PcParams& p, const CUtensorMap& map, int grid, bool cor, IoType io, cudaStream_t s) {
-  if (io == IoType::f16) launch_pass_t<NP, false, __half, PASS>(p, map, grid, s);
-  else if (cor) launch_pass_t<NP, true, float, PASS>(p, map, grid, s);
-  else launch_pass_t<NP, false, float, PASS>(p, map, grid, s);
+template <int NP, bool COR, typename TIo, int SLOT>
+void launch_apply_t(const PcParams& p, const CUtensorMap& map, int grid, cudaStream_t s) {
+  auto kern = pc_apply_kernel<NP, COR, TIo, SLOT>;
+  static std::once_flag once;
+  std::call_once(once, [&] { set_smem(kern, (int)ApplySmem<NP, TIo>::kBytes); });
+  kern<<<grid, 128 * kApWg, ApplySmem<NP, TIo>::kBytes, s>>>(p, map);
+  note_launch();
+  TSQR_CUDA_CHECK(cudaGetLastError());
 }
-template <int PASS>
-void launch_pass(int np, const PcParams& p, const CUtensorMap& map, int grid, bool cor, IoType io, cudaStream_t s) {
-  switch (np) {
-    case 16: launch_pass_np<16, PASS>(p, map, grid, cor, io, s); break;
-    case 32: launch_pass_np<32, PASS>(p, map, grid, cor, io, s); break;
-    default: launch_pass_np<64, PASS>(p, map, grid, cor, io, s); break;
+template <int PASS, int NP, bool COR, typename TIo>
+void launch_slot(int slot, const PcParams& p, const CUtensorMap& map, int grid, cudaStream_t s) {
+  if (PASS == 1) {
+    switch (slot) {
+      case 0: launch_pass1_t<NP, COR, TIo, 0>(p, map, grid, s); break;
+      case 1: launch_pass1_t<NP, COR, TIo, 1>(p, map, grid, s); break;
+      default: launch_pass1_t<NP, COR, TIo, 2>(p, map, grid, s); break;
+    }
+  } else {
+    switch (slot) {
+      case 0: launch_apply_t<NP, COR, TIo, 0>(p, map, grid, s); break;
+      case 1: launch_apply_t<NP, COR, TIo, 1>(p, map, grid, s); break;
+      default: launch_apply_t<NP, COR, TIo, 2>(p, map, grid, s); break;
+    }
   }
+}
+template <int PASS, int NP>
+void launch_np(int slot, const PcParams& p, const CUtensorMap& map, int grid, bool cor, IoType io, cudaStream_t s) {
+  if (io == IoType::f16) launch_slot<PASS, NP, false, __half>(slot, p, map, grid, s);
+  else if (cor) launch_slot<PASS, NP, true, float>(slot, p, map, grid, s);
+  else launch_slot<PASS, NP, false, float>(slot, p, map, grid, s);
+}
+// pass 1 (PASS = 1: pc_pass_kernel, whole-tile TMA box) or pass 2 (PASS = 2: pc_apply_kernel, 128 x 16 boxes)
+template <int PASS>
+void launch_pass(const PcCall& c, PcParams p, bool want_tma, cudaStream_t s) {
+  const int np = c.L.np;
+  CUtensorMap map;
+  memset(&map, 0, sizeof(map));
+  p.use_tma = (want_tma && tma_enabled() && make_tile_map(&map, c.A, c.lda, c.M, c.n, np, c.io, PASS == 2 ? 16 : 0)) ? 1 : 0;
+  int grid = c.L.grid;
+  if (PASS == 2) {   // one CTA of four tile pipelines per SM
+    const int g = (int)std::min<long long>(device_sm_count(), c.L.tiles);
+    p.tiles_per_cta = (int)((c.L.tiles + g - 1) / g);
+    grid = (int)((c.L.tiles + p.tiles_per_cta - 1) / p.tiles_per_cta);
+  }
+  const int slot = img_acquire(c.ws + c.L.cimg, s);
+  switch (np) {
+    case 16: launch_np<PASS, 16>(slot, p, map, grid, c.cor, c.io, s); break;
+    case 32: launch_np<PASS, 32>(slot, p, map, grid, c.cor, c.io, s); break;
+    default: launch_np<PASS, 64>(slot, p, map, grid, c.cor, c.io, s); break;
+  }
+  img_release(slot, s);
 }
 
 template <int NP, typename TIo>
@@ -715,14 +1057,14 @@ void launch_sample_t(const PcCall& c, cudaStream_t s) {
   static std::once_flag once;
   std::call_once(once, [&] { set_smem(kern, (int)SmpCfg<NP>::kBytes); });
   kern<<<1, 8 * NP, SmpCfg<NP>::kBytes, s>>>(reinterpret_cast<const TIo*>(c.A), c.lda, c.M, c.n, c.ws + c.L.rpre,
-                                              reinterpret_cast<int*>(c.ws + c.L.status));
+                                              c.ws + c.L.cimg, reinterpret_cast<int*>(c.ws + c.L.status));
   note_launch();
   TSQR_CUDA_CHECK(cudaGetLastError());
 }
 template <int NP>
 void launch_finish_t(const PcCall& c, cudaStream_t s) {
   auto kern = pc_finish_kernel<NP>;
-  const int bytes = 3 * NP * NP * (int)sizeof(double);
+  const int bytes = 4 * NP * NP * (int)sizeof(double);
   static std::once_flag once;
   std::call_once(once, [&] { set_smem(kern, bytes); });
   const int lanes = (c.cor ? 2 : 1) * NP;
@@ -749,12 +1091,7 @@ PcParams pass_params(const PcCall& c) {
 }
 
 size_t align64(size_t x) { return (x + 63) / 64 * 64; }
-// TSQR_B200_TMA=0 makes the passes load their tiles with per-thread global loads (the path taken anyway when
-// lda * sizeof(element) is not a multiple of 16 bytes)
-bool tma_enabled() {
-  static const bool on = [] { const char* e = std::getenv("TSQR_B200_TMA"); return !(e && e[0] == '0'); }();
-  return on;
-}
+
 
 }  // namespace
 
@@ -773,6 +1110,7 @@ PcLayout pc_layout(long long m, int n) {
   L.rout = off; off = align64(off + np2);
   L.cmat = off; off = align64(off + np2);
   L.rzinv = off; off = align64(off + np2);
+  L.cimg = off; off = align64(off + kImgFloats);
   L.gsum = off; off = align64(off + 2 * (2 * np2));                       // doubles
   // sized for the largest grid any device of this process can ask for (the query may run before a device is chosen)
   const size_t gmax = (size_t)std::max<long long>(L.grid, std::min<long long>(2 * 160, L.tiles));
@@ -791,13 +1129,9 @@ void pc_reduce(const PcCall& c, cudaStream_t s) {
       switch (np) { case 16: launch_sample_t<16, float>(c, s); break; case 32: launch_sample_t<32, float>(c, s); break; default: launch_sample_t<64, float>(c, s); }
     }
   }
-  PcParams p = pass_params(c);
-  CUtensorMap map;
-  memset(&map, 0, sizeof(map));
-  p.use_tma = (tma_enabled() && make_tile_map(&map, c.A, c.lda, c.M, c.n, np, c.io)) ? 1 : 0;
   {
     ProfScope prof(s, 101);
-    launch_pass<1>(np, p, map, c.L.grid, c.cor, c.io, s);
+    launch_pass<1>(c, pass_params(c), true, s);
   }
   {
     ProfScope prof(s, 102);
@@ -816,17 +1150,17 @@ void pc_probe(const PcCall& c, const float* rpre, const float* cmat, double* gsu
   int* status = reinterpret_cast<int*>(c.ws + c.L.status);
   TSQR_CUDA_CHECK(cudaMemsetAsync(status, 0, 16 * sizeof(int), s));
   TSQR_CUDA_CHECK(cudaMemcpyAsync(c.ws + c.L.rpre, rpre, np2 * sizeof(float), cudaMemcpyDeviceToDevice, s));
-  PcParams p = pass_params(c);
-  CUtensorMap map;
-  memset(&map, 0, sizeof(map));
-  p.use_tma = (use_tma && make_tile_map(&map, c.A, c.lda, c.M, c.n, np, c.io)) ? 1 : 0;
-  if (use_tma && !p.use_tma) throw std::runtime_error("tsqr_b200: no TMA map for this matrix (alignment)");
-  launch_pass<1>(np, p, map, c.L.grid, c.cor, c.io, s);
+  pc_cimg_kernel<<<1, 256, 0, s>>>(c.ws + c.L.rpre, c.ws + c.L.cimg, np);
+  if (use_tma) {
+    CUtensorMap probe_map;
+    if (!make_tile_map(&probe_map, c.A, c.lda, c.M, c.n, np, c.io)) throw std::runtime_error("tsqr_b200: no TMA map for this matrix (alignment)");
+  }
+  launch_pass<1>(c, pass_params(c), use_tma, s);
   switch (np) { case 16: launch_finish_t<16>(c, s); break; case 32: launch_finish_t<32>(c, s); break; default: launch_finish_t<64>(c, s); }
   TSQR_CUDA_CHECK(cudaMemcpyAsync(gsum_out, c.ws + c.L.gsum, 2 * np2 * sizeof(double), cudaMemcpyDeviceToDevice, s));
   TSQR_CUDA_CHECK(cudaMemcpyAsync(c.ws + c.L.cmat, cmat, np2 * sizeof(float), cudaMemcpyDeviceToDevice, s));
   pc_set_status_kernel<<<1, 1, 0, s>>>(status, kPcOk);
-  launch_pass<2>(np, p, map, c.L.grid, c.cor, c.io, s);
+  launch_pass<2>(c, pass_params(c), use_tma, s);
 }
 
 void pc_build(const PcCall& c, const float* B, long long ldb, cudaStream_t s) {
@@ -841,11 +1175,7 @@ void pc_build(const PcCall& c, const float* B, long long ldb, cudaStream_t s) {
     note_launch();
     TSQR_CUDA_CHECK(cudaGetLastError());
   }
-  PcParams p = pass_params(c);
-  CUtensorMap map;
-  memset(&map, 0, sizeof(map));
-  p.use_tma = (tma_enabled() && make_tile_map(&map, c.A, c.lda, c.M, c.n, np, c.io)) ? 1 : 0;
-  launch_pass<2>(np, p, map, c.L.grid, c.cor, c.io, s);
+  launch_pass<2>(c, pass_params(c), true, s);
 }
 
 }  // namespace tsqr_b200

@@ -1,6 +1,6 @@
 // Preconditioned-Cholesky TSQR ("PC" path): the fast path of every *_tc_* compute mode on tall matrices.
 //
-//   sample : R_pre = R factor of a Householder QR of h = 8 NP rows of A taken at a fixed stride
+//   sample : R_pre = R factor of a Householder QR of h = 8 NP rows of A (h / 16 clusters of 16 rows, evenly spread)
 //   pass 1 : Z = A R_pre^-1 (blocked forward substitution, never an explicit inverse), G = Z^T Z,
 //            accumulated per CTA;  A is only read
 //   finish : G = sum of the CTA partials (fp64), R_z = chol(G), certificate
@@ -36,6 +36,7 @@ struct PcLayout {
   size_t rout = 0;     // n x n fp32, ld n  (the R of this call, from whichever path produced it)
   size_t cmat = 0;     // NP x NP fp32, ld NP: C of pass 2
   size_t rzinv = 0;    // NP x NP fp32, ld NP: R_z^-1
+  size_t cimg = 0;     // staging copy of the constant-memory image of R_pre's diagonal blocks
   size_t gpart = 0;    // [grid][NP][128] doubles
   size_t gsum = 0;     // [2 NP][NP] doubles
   size_t total = 0;
