@@ -95,6 +95,16 @@ def test_fast_path_uncorrected_modes(cuda, oracle, mode):
     assert st == 1 and orth < 5e-3 and res < 5e-3 and rd < 5e-3
 
 
+@pytest.mark.parametrize("mode", ["fp32_tc_nocor", "fp16_tc_nocor"])
+def test_fast_path_uncorrected_modes_conditioned(cuda, oracle, mode):
+    """kappa = 1e6 in a mode whose products carry 2^-11 errors: Q stays orthogonal to the mode's level only if both
+    passes compute bit-identical Z = A R_pre^-1 (their difference would be amplified by cond(R_pre))."""
+    a = oracle.latms_matrix(1 << 17, 64, 1e6, seed=33)
+    st, est, orth, res, _ = _run(oracle, a, mode)
+    print(f"{mode} cond 1e6: status {st} est {est:.3f} orth {orth:.2e} res {res:.2e}")
+    assert orth < 5e-3 and res < 5e-3
+
+
 @pytest.mark.parametrize("cond", [1e3, 1e6])
 def test_fast_path_conditioned(cuda, oracle, cond):
     a = oracle.latms_matrix(1 << 17, 64, cond, seed=31)

@@ -410,7 +410,9 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
       if (p < NPAN - 1 || PASS == 2) {   // Z_p -> tensor memory as the A operand of the products that follow
         float zh[16], zl[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) { zh[i] = COR ? to_tf32_rna(y[16 * p + i]) : y[16 * p + i]; zl[i] = __fsub_rn(y[16 * p + i], zh[i]); }
+        // rounded to tf32 in EVERY mode, exactly as pc_apply_kernel stores its operand: the two passes must compute
+        // bit-identical Z (a difference of 2^-11 between them is amplified by cond(R_pre) in Q = Z C)
+        for (int i = 0; i < 16; ++i) { zh[i] = to_tf32_rna(y[16 * p + i]); zl[i] = __fsub_rn(y[16 * p + i], zh[i]); }
         tmem_st16(tmem_addr(tmZh, warp, 16 * p), zh);
         if (COR) tmem_st16(tmem_addr(tmZl, warp, 16 * p), zl);
         tmem_wait_st();
@@ -597,6 +599,11 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
   if (use_tma && t == 0)
     for (int g = 0; g < S && g < npanels; ++g) issue_load(g);
   uint32_t ph_mma = 0;
+  // operand descriptors: fixed per warp group; thread 0 spent more cycles building them per panel than the
+  // tensor pipe spent on the products (measured with phase clocks: 6500 of 16500 cycles per tile)
+  const uint64_t dZh = smem_desc(smem_u32(ZHi), 2048, 128), dZl = smem_desc(smem_u32(ZLo), 2048, 128);
+  const uint64_t dRh = smem_desc(smem_u32(RbHi), 128, 512), dRl = smem_desc(smem_u32(RbLo), 128, 512);
+  const uint64_t dCh = smem_desc(smem_u32(CHi), 128, kb::sbo(NP)), dCl = smem_desc(smem_u32(CLo), 128, kb::sbo(NP));
 
   for (int it = 0; it < ntl; ++it) {
     const int tile = tile_of(it);
@@ -647,18 +654,16 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
       }
       fence_before_sync();
       named_bar_sync(1 + wg, 128);
-      if (t == 0) {
+      if (t == 0) {   // 12 products per panel: hoisted descriptors plus compile-time deltas of the address field
         fence_after_sync();
-        const uint32_t zh = smem_u32(ZHi), zl = smem_u32(ZLo);
         if (p < NPAN - 1) {   // U[:, 16(p+1):] (+)= Z_p R[p, 16(p+1):]
           const int N = NP - 16 * (p + 1);
           const uint32_t id = idesc_tf32(128, N, false, false, false);
-          const uint32_t bh = smem_u32(RbHi) + rblk_off<NP>(p), bl = smem_u32(RbLo) + rblk_off<NP>(p);
           const uint32_t d = tmU + 16 * p;
 #pragma unroll
           for (int kk = 0; kk < 2; ++kk) {
-            const uint64_t ah = smem_desc(zh + kk * 4096, 2048, 128), al = smem_desc(zl + kk * 4096, 2048, 128);
-            const uint64_t dh = smem_desc(bh + kk * 256, 128, 512), dl = smem_desc(bl + kk * 256, 128, 512);
+            const uint64_t ah = dZh + (uint64_t)(kk * (4096 >> 4)), al = dZl + (uint64_t)(kk * (4096 >> 4));
+            const uint64_t dh = dRh + (uint64_t)((rblk_off<NP>(p) + kk * 256) >> 4), dl = dRl + (uint64_t)((rblk_off<NP>(p) + kk * 256) >> 4);
             mma_tf32(d, ah, dh, id, p > 0 || kk > 0);
             if (COR) {
               mma_tf32(d, ah, dl, id, true);
@@ -668,11 +673,10 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
         }
         {   // Q (+)= Z_p C[16p : 16p+16, :]
           const uint32_t id = idesc_tf32(128, NP, false, false, false);
-          const uint32_t ch = smem_u32(CHi) + p * 512, cl = smem_u32(CLo) + p * 512;
 #pragma unroll
           for (int kk = 0; kk < 2; ++kk) {
-            const uint64_t ah = smem_desc(zh + kk * 4096, 2048, 128), al = smem_desc(zl + kk * 4096, 2048, 128);
-            const uint64_t dh = smem_desc(ch + kk * 256, 128, kb::sbo(NP)), dl = smem_desc(cl + kk * 256, 128, kb::sbo(NP));
+            const uint64_t ah = dZh + (uint64_t)(kk * (4096 >> 4)), al = dZl + (uint64_t)(kk * (4096 >> 4));
+            const uint64_t dh = dCh + (uint64_t)((p * 512 + kk * 256) >> 4), dl = dCl + (uint64_t)((p * 512 + kk * 256) >> 4);
             mma_tf32(tmD, ah, dh, id, p > 0 || kk > 0);
             if (COR) {
               mma_tf32(tmD, ah, dl, id, true);
@@ -689,18 +693,17 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
     fence_after_sync();
     TIo* qp = Q + row;
     const bool full = (n == NP) && ((long long)(tile + 1) * kPcTileRows <= P.M);
+    uint32_t qr[NP];   // all loads of the accumulator row in flight behind one wait
 #pragma unroll
-    for (int c0 = 0; c0 < NP; c0 += 16) {
-      float qv[16];
-      tmem_ld16(tmem_addr(tmD, warp, c0), qv);
-      if (full) {
+    for (int c0 = 0; c0 < NP; c0 += 16) tmem_ld16_nowait(tmem_addr(tmD, warp, c0), qr + c0);
+    tmem_wait_ld();
+    if (full) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) io_store(qp + (long long)(c0 + i) * P.ldq, qv[i]);
-      } else {
+      for (int c = 0; c < NP; ++c) io_store(qp + (long long)c * P.ldq, __uint_as_float(qr[c]));
+    } else {
 #pragma unroll
-        for (int i = 0; i < 16; ++i)
-          if (valid && c0 + i < n) io_store(qp + (long long)(c0 + i) * P.ldq, qv[i]);
-      }
+      for (int c = 0; c < NP; ++c)
+        if (valid && c < n) io_store(qp + (long long)c * P.ldq, __uint_as_float(qr[c]));
     }
   }
   fence_before_sync();
