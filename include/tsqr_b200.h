@@ -103,6 +103,19 @@ int tsqr_b200_pc_probe(int mode, const void* a, size_t lda, size_t m, size_t n, 
                        void* q, size_t ldq, double* gsum, int use_tma, void* workspace, size_t workspace_bytes,
                        void* stream);
 
+/* TSQR of A (m x n, n <= 64) for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc). No counterpart in the reference.
+ * Same result as tsqr_b200_tsqr, but the workspace is a file-scope static __device__ array of
+ * TSQR_B200_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it until the process
+ * exits); the call allocates and frees nothing. A (mode, m, n) whose level plan needs more than that is rejected
+ * with TSQR_B200_ERR_ARGUMENT (tsqr_b200_last_error() names both numbers): 64 MiB admits every *_tc_* mode at any m
+ * (their workspace is bounded by the SM count: 40 MB at n = 64) and the CUDA-core modes (*_notc, *_emu; one R checkpoint
+ * per 128-row tile) up to about 2^18 rows at n = 64, 2^24 rows at n = 16. ALL calls on a device share the one array: calls that overlap on the GPU (different streams, different
+ * threads) race -- serialise them. The array keeps the previous call's contents; nothing in it needs clearing. */
+#define TSQR_B200_STATIC_SCRATCH_BYTES (64u << 20)
+int tsqr_b200_tsqr_static(int mode, void* q, size_t ldq, void* r, size_t ldr, const void* a, size_t lda,
+                          size_t m, size_t n, void* stream);
+
 /* how many kernels this library has launched in this process (bench bookkeeping) */
 unsigned long long tsqr_b200_launch_count(void);
 

@@ -30,6 +30,7 @@ SIGNATURES = {
     "tsqr_b200_mode_uses_tensor_cores": (_c.c_int, [_c.c_int, _sz]),
     "tsqr_b200_pc_status": (_c.c_int, [_c.c_int, _sz, _sz, _vp, _vp, _vp]),
     "tsqr_b200_pc_probe": (_c.c_int, [_c.c_int, _vp, _sz, _sz, _sz, _vp, _vp, _vp, _sz, _vp, _c.c_int, _vp, _sz, _vp]),
+    "tsqr_b200_tsqr_static": (_c.c_int, [_c.c_int, _vp, _sz, _vp, _sz, _vp, _sz, _sz, _sz, _vp]),
     "tsqr_b200_selftest_mma": (_c.c_int, [_c.c_int, _c.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 

@@ -10,8 +10,10 @@
 #include <atomic>
 #include <cmath>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <dlfcn.h>
+#include <mutex>
 
 namespace tsqr_b200 {
 static std::atomic<unsigned long long> g_launches{0};
@@ -180,6 +182,53 @@ int tsqr_b200_qr32x16_batched(int mode, void* q, size_t ldq, void* r, size_t ldr
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ TSQR without any allocation
+// Workspace of tsqr_b200_tsqr_static: a file-scope array in device memory. Every GPU that loads the library holds
+// these TSQR_B200_STATIC_SCRATCH_BYTES until the process exits. In HOST code the name below is only a stand-in for
+// the symbol, not a device address: the address is looked up with cudaGetSymbolAddress once per device (with that
+// device current) and that pointer is what the kernels get.
+static __device__ __align__(256) unsigned char g_static_scratch[TSQR_B200_STATIC_SCRATCH_BYTES];
+
+namespace {
+float* static_scratch_address() {
+  static std::mutex mu;
+  static void* ptrs[64] = {};
+  int dev = 0;
+  TSQR_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) throw std::runtime_error("tsqr_b200: device index out of range for the static scratch table");
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    TSQR_CUDA_CHECK(cudaGetSymbolAddress(&p, g_static_scratch));
+    if (!p || (reinterpret_cast<uintptr_t>(p) & 255u) != 0) throw std::runtime_error("tsqr_b200: bad static scratch address");
+    ptrs[dev] = p;
+  }
+  return reinterpret_cast<float*>(ptrs[dev]);
+}
+}  // namespace
+
+extern "C" int tsqr_b200_tsqr_static(int mode, void* q, size_t ldq, void* r, size_t ldr, const void* a, size_t lda, size_t m,
+                                     size_t n, void* stream) {
+  if (!mode_valid(mode)) { set_err("invalid compute mode"); return TSQR_B200_ERR_ARGUMENT; }
+  if (m == 0 || n == 0 || n > (size_t)kMaxN || n > m) return TSQR_B200_INVALID_SIZE;
+  if (!q || !r || !a) { set_err("null pointer argument"); return TSQR_B200_ERR_ARGUMENT; }
+  const size_t need = make_plan_for(mode, (long long)m, (int)n).total_floats * sizeof(float);   // this mode's plan only
+  if (need > (size_t)TSQR_B200_STATIC_SCRATCH_BYTES) {
+    char msg[256];
+    std::snprintf(msg, sizeof(msg), "%zu x %zu in mode %d needs %zu bytes of workspace, the static scratch array holds %zu: use "
+                  "tsqr_b200_tsqr with a caller-provided workspace", m, n, mode, need, (size_t)TSQR_B200_STATIC_SCRATCH_BYTES);
+    set_err(msg);
+    return TSQR_B200_ERR_ARGUMENT;
+  }
+  return guarded([&] {
+    // Nothing in the workspace has to start at zero: the first kernel of a call resets the status words it uses and
+    // every other word is written before it is read, so the previous call's contents are harmless.
+    tsqr_full(mode, q, (long long)ldq, r, (long long)ldr, a, (long long)lda, (long long)m, (int)n, static_scratch_address(),
+              (size_t)TSQR_B200_STATIC_SCRATCH_BYTES, (cudaStream_t)stream);
+    return 0;
+  });
+}
 
 // ------------------------------------------------------------------ mtk:: C++ API
 namespace {
