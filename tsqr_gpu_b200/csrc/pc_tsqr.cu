@@ -36,7 +36,7 @@ struct PcParams {
   const float* C;        // pass 2
   double* Gpart;         // pass 1
   int* status;
-  int tiles, tiles_per_cta, use_tma;
+  int tiles, tiles_per_cta, use_tma, use_tma_q;
 };
 
 // Image of R_pre's diagonal blocks for the forward substitution, in CONSTANT memory: [k][16] = -R[k][16 (k/16) + j]
@@ -241,6 +241,36 @@ __global__ void __launch_bounds__(8 * NP, 1) pc_sample_kernel(const TIo* __restr
   }
 }
 
+// z R_pp = y for one 16-column panel of one matrix row (forward substitution along the row), shared by both passes so
+// that they produce bit-identical Z. ci = constant-memory image of R_pre (-R_pp strictly above the diagonal, zero
+// elsewhere; 1 / diag at kImgInv). Adjacent columns (y_2k, y_2k+1) are updated by ONE packed fma.rn.f32x2 whose
+// operands are z (register, broadcast form) and the pair (c_2k, c_2k+1) (uniform register pair loaded by LDCU): 64
+// FFMA2 + 16 FMUL per panel instead of 120 FFMA + 16 FMUL, no load instruction, IEEE per element (same bits as the
+// scalar form). For an even pivot i the pair (i, i+1) is included: its first constant is zero, fma(z, 0, z) = z.
+__device__ __forceinline__ void solve_panel16(float (&y)[16], const float* __restrict__ ci, int p) {
+  f32x2 yp[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) yp[k] = pack2(y[2 * k], y[2 * k + 1]);
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    float lo, hi;
+    unpack2(yp[i / 2], lo, hi);
+    const float z = __fmul_rn((i & 1) ? hi : lo, ci[kImgInv + 16 * p + i]);
+    yp[i / 2] = (i & 1) ? pack2(lo, z) : pack2(z, hi);
+    const f32x2 zz = pack2(z, z);
+#pragma unroll
+    for (int j2 = (i + 1) / 2; j2 < 8; ++j2) {
+      if (2 * j2 + 1 <= i) continue;
+      const f32x2 cc = pack2(ci[(16 * p + i) * 16 + 2 * j2], ci[(16 * p + i) * 16 + 2 * j2 + 1]);
+      yp[j2] = fma2(zz, cc, yp[j2]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) unpack2(yp[k], y[2 * k], y[2 * k + 1]);
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) { f32x2 d; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ f32x2 addp2(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+
 // ======================================================================================= passes
 template <int NP>
 __host__ __device__ constexpr uint32_t rblk_off(int p) {   // byte offset of R block p (rows [16p, 16p+16), cols >= 16(p+1))
@@ -340,7 +370,10 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
       float g[16];
       tmem_ld16(tmem_addr(tmD, warp, c0), g);
 #pragma unroll
-      for (int i = 0; i < 16; ++i) acc[c0 + i] = __fadd_rn(acc[c0 + i], g[i]);
+      for (int i = 0; i < 16; i += 2) {
+        const f32x2 d = addp2(pack2(acc[c0 + i], acc[c0 + i + 1]), pack2(g[i], g[i + 1]));
+        unpack2(d, acc[c0 + i], acc[c0 + i + 1]);
+      }
     }
   };
   auto flush = [&]() {
@@ -397,16 +430,13 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
         float u[16];
         tmem_ld16(tmem_addr(tmU, warp, 16 * p), u);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) y[16 * p + i] = __fsub_rn(y[16 * p + i], u[i]);
+        for (int i = 0; i < 16; i += 2) {
+          const f32x2 d = sub2(pack2(y[16 * p + i], y[16 * p + i + 1]), pack2(u[i], u[i + 1]));
+          unpack2(d, y[16 * p + i], y[16 * p + i + 1]);
+        }
       }
-      // z_p R_pp = y_p : forward substitution along the row, -R_pp and 1 / diag as constant-bank operands
-#pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const float z = __fmul_rn(y[16 * p + i], ci[kImgInv + 16 * p + i]);
-        y[16 * p + i] = z;
-#pragma unroll
-        for (int j = i + 1; j < 16; ++j) y[16 * p + j] = __fmaf_rn(z, ci[(16 * p + i) * 16 + j], y[16 * p + j]);
-      }
+      // z_p R_pp = y_p : forward substitution along the row (packed, constants as uniform-register operands)
+      solve_panel16(*reinterpret_cast<float(*)[16]>(&y[16 * p]), ci, p);
       if (p < NPAN - 1 || PASS == 2) {   // Z_p -> tensor memory as the A operand of the products that follow
         float zh[16], zl[16];
 #pragma unroll
@@ -508,19 +538,21 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
   if (warp == 0) tmem_dealloc<256>(tm);
 }
 
-// ======================================================================================= pass 2, v2
-// Q = (A R_pre^-1) C with FOUR tiles in flight per SM: one CTA of 4 warp groups per SM, each warp group an
-// independent 128-row tile pipeline. What makes four fit where pc_pass_kernel<2> holds two:
-//   * the Z_p operand of the tcgen05 products is staged in shared memory (row-wise "rn" layout, 16 KB per warp
-//     group, reused panel after panel), so a tile needs 112 TMEM columns (U: 48, Q accumulator: 64), not 256;
-//   * the tile lands panel by panel (TMA boxes of 128 x 16 into a ring of kApSlots slots per warp group) and is
-//     consumed panel by panel: 16 values per thread live instead of 64, ~100 registers;
-//   * Q accumulates panel by panel: D += Z_p C[16p : 16p+16, :] is issued together with the substitution update
-//     U += Z_p R[p, trail], so nothing of Z outlives its panel.
-// A landing slot is handed back after the panel's Z stores -- every loaded value has been consumed by then, which
-// is the ordering the TMA (async proxy) write needs (see the note in pc_pass_kernel).
+// ======================================================================================= pass 2
+// Q = (A R_pre^-1) C with THREE tiles in flight per SM: one CTA of 3 warp groups per SM, each warp group an
+// independent 128-row tile pipeline that works panel by panel (16 columns):
+//   * the tile lands panel by panel (TMA boxes of 128 x 16 into a ring of kApSlots slots per warp group);
+//   * the solved panel Z_p goes to TENSOR MEMORY (tcgen05.st, hi | lo: 32 columns, reused panel after panel) and is
+//     the A operand of both products of the panel: U += Z_p R[p, trail] (substitution update) and
+//     D += Z_p C[16p : 16p+16, :] (Q accumulates panel by panel, nothing of Z outlives its panel). With Z_p staged
+//     in shared memory instead (measured) every corrected product re-reads a 4 KB operand slice: 400 KB of
+//     shared-memory traffic per tile, which bounded the kernel; from tensor memory the A operand costs nothing;
+//   * a tile needs 144 TMEM columns (U 48, D 64, Z_p 32): three tiles per SM;
+//   * Q leaves through shared memory and ONE TMA store per tile (no per-column address arithmetic, no 64 strided
+//     stores per thread); when ldq does not allow a tensor map the threads store their rows themselves.
 constexpr int kApSlots = 3;
-constexpr int kApWg = 4;
+constexpr int kApWg = 3;
+constexpr int kApTmemPerWg = 160;   // 144 used: U [0, 48), D [48, 112), Z hi [112, 128), Z lo [128, 144)
 template <int NP, typename TIo>
 struct ApplySmem {
   static constexpr int NPAN = NP / 16;
@@ -532,14 +564,15 @@ struct ApplySmem {
   static constexpr uint32_t oBar = oRblkLo + kRblk;                      // per warp group: full[S], empty[S], mma; then the tmem slot
   static constexpr uint32_t kBarBytes = 256;
   static constexpr uint32_t kSlot = 128u * 16u * sizeof(TIo);           // one landed panel
-  static constexpr uint32_t kZop = rn::bytes(16);                        // 8192: one 128 x 16 operand (hi or lo)
-  static constexpr uint32_t kWg = kApSlots * kSlot + 2 * kZop;
+  static constexpr uint32_t kQst = 128u * NP * sizeof(TIo);             // Q tile staging for the TMA store, [column][row]
+  static constexpr uint32_t kWg = kApSlots * kSlot + kQst;
   static constexpr uint32_t oWg = (oBar + kBarBytes + 1023) / 1024 * 1024;
   static constexpr uint32_t kBytes = oWg + kApWg * kWg;
 };
 
 template <int NP, bool COR, typename TIo, int SLOT>
-__global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams P, const __grid_constant__ CUtensorMap tmapP) {
+__global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams P, const __grid_constant__ CUtensorMap tmapP,
+                                                                 const __grid_constant__ CUtensorMap tmapQ) {
   using Sm = ApplySmem<NP, TIo>;
   constexpr int NPAN = NP / 16, S = kApSlots;
   extern __shared__ __align__(1024) char sm[];
@@ -556,21 +589,23 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
   uint64_t* bar_mma = bars + 2 * S;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + Sm::oBar + Sm::kBarBytes - 8);
   char* wgbase = sm + Sm::oWg + wg * Sm::kWg;
-  char* ZHi = wgbase + S * Sm::kSlot;
-  char* ZLo = ZHi + Sm::kZop;
+  TIo* qst = reinterpret_cast<TIo*>(wgbase + S * Sm::kSlot);
   const int n = P.n;
   const TIo* A = reinterpret_cast<const TIo*>(P.A);
   TIo* Q = reinterpret_cast<TIo*>(P.Q);
-  const bool use_tma = P.use_tma != 0;
+  const bool use_tma = P.use_tma != 0, tma_q = P.use_tma_q != 0;
 
   if (tid < 32) tmem_alloc<512>(tmem_slot);
   if (t == 0) {
     for (int i = 0; i < S; ++i) { mbar_init(bar_full + i, 1); mbar_init(bar_empty + i, 128); }
     mbar_init(bar_mma, 1);
     fence_mbar_init();
-    if (use_tma && wg == 0) tma_prefetch_desc(&tmapP);
+    if (wg == 0) {
+      if (use_tma) tma_prefetch_desc(&tmapP);
+      if (tma_q) tma_prefetch_desc(&tmapQ);
+    }
   }
-  for (int idx = tid; idx < NP * NP; idx += 128 * kApWg) {   // operand images of R_pre and C
+  for (int idx = tid; idx < NP * NP; idx += 128 * kApWg) {   // operand images of R_pre (off-diagonal blocks) and C
     const int k = idx % NP, c = idx / NP;
     const float v = P.Rpre[idx];
     const int pk = k >> 4, pc = c >> 4;
@@ -581,10 +616,10 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t tm = *tmem_slot + 128u * wg;
-  const uint32_t tmU = tm, tmD = tm + 64;   // U column of tile column c (>= 16): tmU + c - 16
-
-  // this warp group's tiles: every kApWg-th tile of the CTA's range, walked backwards (see pc_pass_kernel)
+  const uint32_t tm = *tmem_slot + (uint32_t)(kApTmemPerWg * wg);
+  const uint32_t tmU = tm, tmD = tm + 48, tmZh = tm + 112, tmZl = tm + 128;   // U column of tile column c (>= 16): tmU + c - 16
+  // this warp group's tiles: every kApWg-th tile of the CTA's range, walked backwards (the rows this CTA read last
+  // in pass 1 are the likeliest to be in L2)
   const int tile_beg = blockIdx.x * P.tiles_per_cta;
   const int tile_end = min(tile_beg + P.tiles_per_cta, P.tiles);
   const int ntl_cta = max(tile_end - tile_beg, 0);
@@ -599,9 +634,7 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
   if (use_tma && t == 0)
     for (int g = 0; g < S && g < npanels; ++g) issue_load(g);
   uint32_t ph_mma = 0;
-  // operand descriptors: fixed per warp group; thread 0 spent more cycles building them per panel than the
-  // tensor pipe spent on the products (measured with phase clocks: 6500 of 16500 cycles per tile)
-  const uint64_t dZh = smem_desc(smem_u32(ZHi), 2048, 128), dZl = smem_desc(smem_u32(ZLo), 2048, 128);
+  // B operand descriptors: fixed per CTA, everything else is a compile-time delta of the address field
   const uint64_t dRh = smem_desc(smem_u32(RbHi), 128, 512), dRl = smem_desc(smem_u32(RbLo), 128, 512);
   const uint64_t dCh = smem_desc(smem_u32(CHi), 128, kb::sbo(NP)), dCl = smem_desc(smem_u32(CLo), 128, kb::sbo(NP));
 
@@ -623,29 +656,29 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
 #pragma unroll
         for (int i = 0; i < 16; ++i) y[i] = (valid && 16 * p + i < n) ? io_plain(ap + (long long)i * P.lda) : 0.f;
       }
-      if (p > 0 || it > 0) {   // the products that read Z_{p-1} (and, for p = 0, the previous tile's) are complete
-        if (p > 0) {
-          mbar_wait(bar_mma, ph_mma);
-          ph_mma ^= 1;
-          fence_after_sync();
-          float u[16];
-          tmem_ld16(tmem_addr(tmU, warp, 16 * (p - 1)), u);
+      if (p > 0) {   // y_p -= sum_{q<p} Z_q R[q, p]; all products of panel p-1 are complete after this wait
+        mbar_wait(bar_mma, ph_mma);
+        ph_mma ^= 1;
+        fence_after_sync();
+        float u[16];
+        tmem_ld16(tmem_addr(tmU, warp, 16 * (p - 1)), u);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) y[i] = __fsub_rn(y[i], u[i]);
+        for (int i = 0; i < 16; i += 2) {
+          const f32x2 d = sub2(pack2(y[i], y[i + 1]), pack2(u[i], u[i + 1]));
+          unpack2(d, y[i], y[i + 1]);
         }
       }
-      // z_p R_pp = y_p, -R_pp and 1 / diag as constant-bank operands
+      solve_panel16(y, ci, p);
+      {   // Z_p -> tensor memory, rounded exactly as pass 1 rounds it (both passes must compute the same Z)
+        float zh[16], zl[16];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const float z = __fmul_rn(y[i], ci[kImgInv + 16 * p + i]);
-        y[i] = z;
-#pragma unroll
-        for (int j = i + 1; j < 16; ++j) y[j] = __fmaf_rn(z, ci[(16 * p + i) * 16 + j], y[j]);
+        for (int i = 0; i < 16; ++i) { zh[i] = to_tf32_rna(y[i]); zl[i] = __fsub_rn(y[i], zh[i]); }
+        tmem_st16(tmem_addr(tmZh, warp, 0), zh);
+        if (COR) tmem_st16(tmem_addr(tmZl, warp, 0), zl);
+        tmem_wait_st();
       }
-#pragma unroll
-      for (int c4 = 0; c4 < 4; ++c4) rn::store4<COR>(ZHi, ZLo, t, c4, y[4 * c4], y[4 * c4 + 1], y[4 * c4 + 2], y[4 * c4 + 3]);
-      fence_async_smem();
-      if (use_tma) {   // every value of the slot has been consumed (the stores above depend on all of them)
+      if (use_tma) {   // hand the slot back: every loaded value has been consumed by the solve above; the fence
+        fence_async_smem();   // orders the generic-proxy reads before the async-proxy write that reuses the slot
         mbar_arrive(bar_empty + slot);
         if (t == 0 && g + S < npanels) {
           mbar_wait(bar_empty + slot, (uint32_t)(g / S) & 1u);
@@ -654,7 +687,7 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
       }
       fence_before_sync();
       named_bar_sync(1 + wg, 128);
-      if (t == 0) {   // 12 products per panel: hoisted descriptors plus compile-time deltas of the address field
+      if (t == 0) {   // up to 12 products per panel
         fence_after_sync();
         if (p < NPAN - 1) {   // U[:, 16(p+1):] (+)= Z_p R[p, 16(p+1):]
           const int N = NP - 16 * (p + 1);
@@ -662,12 +695,11 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
           const uint32_t d = tmU + 16 * p;
 #pragma unroll
           for (int kk = 0; kk < 2; ++kk) {
-            const uint64_t ah = dZh + (uint64_t)(kk * (4096 >> 4)), al = dZl + (uint64_t)(kk * (4096 >> 4));
             const uint64_t dh = dRh + (uint64_t)((rblk_off<NP>(p) + kk * 256) >> 4), dl = dRl + (uint64_t)((rblk_off<NP>(p) + kk * 256) >> 4);
-            mma_tf32(d, ah, dh, id, p > 0 || kk > 0);
+            mma_tf32_ts(d, tmZh + 8 * kk, dh, id, p > 0 || kk > 0);
             if (COR) {
-              mma_tf32(d, ah, dl, id, true);
-              mma_tf32(d, al, dh, id, true);
+              mma_tf32_ts(d, tmZh + 8 * kk, dl, id, true);
+              mma_tf32_ts(d, tmZl + 8 * kk, dh, id, true);
             }
           }
         }
@@ -675,42 +707,52 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
           const uint32_t id = idesc_tf32(128, NP, false, false, false);
 #pragma unroll
           for (int kk = 0; kk < 2; ++kk) {
-            const uint64_t ah = dZh + (uint64_t)(kk * (4096 >> 4)), al = dZl + (uint64_t)(kk * (4096 >> 4));
             const uint64_t dh = dCh + (uint64_t)((p * 512 + kk * 256) >> 4), dl = dCl + (uint64_t)((p * 512 + kk * 256) >> 4);
-            mma_tf32(tmD, ah, dh, id, p > 0 || kk > 0);
+            mma_tf32_ts(tmD, tmZh + 8 * kk, dh, id, p > 0 || kk > 0);
             if (COR) {
-              mma_tf32(tmD, ah, dl, id, true);
-              mma_tf32(tmD, al, dh, id, true);
+              mma_tf32_ts(tmD, tmZh + 8 * kk, dl, id, true);
+              mma_tf32_ts(tmD, tmZl + 8 * kk, dh, id, true);
             }
           }
         }
         mma_commit(bar_mma);
       }
     }
-    // Q tile
+    // ---- Q tile: accumulator row -> (shared memory -> one TMA store) or straight to global memory
+    if (tma_q && it > 0) {   // the staging buffer is free once the previous tile's store has read it
+      if (t == 0) tma_store_wait_read();
+      named_bar_sync(1 + wg, 128);
+    }
     mbar_wait(bar_mma, ph_mma);
     ph_mma ^= 1;
     fence_after_sync();
-    TIo* qp = Q + row;
-    const bool full = (n == NP) && ((long long)(tile + 1) * kPcTileRows <= P.M);
     uint32_t qr[NP];   // all loads of the accumulator row in flight behind one wait
 #pragma unroll
     for (int c0 = 0; c0 < NP; c0 += 16) tmem_ld16_nowait(tmem_addr(tmD, warp, c0), qr + c0);
     tmem_wait_ld();
-    if (full) {
+    if (tma_q) {
 #pragma unroll
-      for (int c = 0; c < NP; ++c) io_store(qp + (long long)c * P.ldq, __uint_as_float(qr[c]));
+      for (int c = 0; c < NP; ++c) io_store(qst + c * 128 + t, __uint_as_float(qr[c]));
+      fence_async_smem();
+      named_bar_sync(1 + wg, 128);
+      if (t == 0) {   // rows beyond M and columns beyond n are clipped by the tensor map
+        tma_store_2d(&tmapQ, qst, tile * kPcTileRows, 0);
+        tma_store_commit();
+      }
     } else {
+      TIo* qp = Q + row;
 #pragma unroll
-      for (int c = 0; c < NP; ++c)
-        if (valid && c < n) io_store(qp + (long long)c * P.ldq, __uint_as_float(qr[c]));
+      for (int c = 0; c < NP; ++c) {
+        if (valid && c < n) io_store(qp, __uint_as_float(qr[c]));
+        qp += P.ldq;
+      }
     }
   }
+  if (tma_q && t == 0) tma_store_wait_all();
   fence_before_sync();
   __syncthreads();
   if (tid < 32) tmem_dealloc<512>(*tmem_slot);
 }
-
 // ======================================================================================= finish
 // Stage 1, every CTA: fp64 sum of the per-CTA partials for 32 consecutive accumulator lanes of one Gram column
 // (warp w adds partials w, w + 8, ...: coalesced 256-byte reads, then the 8 warp sums are added in fixed order).
@@ -993,7 +1035,7 @@ void img_release(int slot, cudaStream_t s) {
 }
 
 template <int NP, bool COR, typename TIo, int SLOT>
-void launch_pass1_t(const PcParams& p, const CUtensorMap& map, int grid, cudaStream_t s) {
+void launch_pass1_t(const PcParams& p, const CUtensorMap& map, const CUtensorMap&, int grid, cudaStream_t s) {
   auto kern = pc_pass_kernel<NP, COR, TIo, 1, SLOT>;
   static std::once_flag once;
   std::call_once(once, [&] { set_smem(kern, (int)PassSmem<NP, 1>::kBytes); });
@@ -1002,54 +1044,56 @@ void launch_pass1_t(const PcParams& p, const CUtensorMap& map, int grid, cudaStr
   TSQR_CUDA_CHECK(cudaGetLastError());
 }
 template <int NP, bool COR, typename TIo, int SLOT>
-void launch_apply_t(const PcParams& p, const CUtensorMap& map, int grid, cudaStream_t s) {
+void launch_apply_t(const PcParams& p, const CUtensorMap& map, const CUtensorMap& mapq, int grid, cudaStream_t s) {
   auto kern = pc_apply_kernel<NP, COR, TIo, SLOT>;
   static std::once_flag once;
   std::call_once(once, [&] { set_smem(kern, (int)ApplySmem<NP, TIo>::kBytes); });
-  kern<<<grid, 128 * kApWg, ApplySmem<NP, TIo>::kBytes, s>>>(p, map);
+  kern<<<grid, 128 * kApWg, ApplySmem<NP, TIo>::kBytes, s>>>(p, map, mapq);
   note_launch();
   TSQR_CUDA_CHECK(cudaGetLastError());
 }
 template <int PASS, int NP, bool COR, typename TIo>
-void launch_slot(int slot, const PcParams& p, const CUtensorMap& map, int grid, cudaStream_t s) {
+void launch_slot(int slot, const PcParams& p, const CUtensorMap& map, const CUtensorMap& mapq, int grid, cudaStream_t s) {
   if (PASS == 1) {
     switch (slot) {
-      case 0: launch_pass1_t<NP, COR, TIo, 0>(p, map, grid, s); break;
-      case 1: launch_pass1_t<NP, COR, TIo, 1>(p, map, grid, s); break;
-      default: launch_pass1_t<NP, COR, TIo, 2>(p, map, grid, s); break;
+      case 0: launch_pass1_t<NP, COR, TIo, 0>(p, map, mapq, grid, s); break;
+      case 1: launch_pass1_t<NP, COR, TIo, 1>(p, map, mapq, grid, s); break;
+      default: launch_pass1_t<NP, COR, TIo, 2>(p, map, mapq, grid, s); break;
     }
   } else {
     switch (slot) {
-      case 0: launch_apply_t<NP, COR, TIo, 0>(p, map, grid, s); break;
-      case 1: launch_apply_t<NP, COR, TIo, 1>(p, map, grid, s); break;
-      default: launch_apply_t<NP, COR, TIo, 2>(p, map, grid, s); break;
+      case 0: launch_apply_t<NP, COR, TIo, 0>(p, map, mapq, grid, s); break;
+      case 1: launch_apply_t<NP, COR, TIo, 1>(p, map, mapq, grid, s); break;
+      default: launch_apply_t<NP, COR, TIo, 2>(p, map, mapq, grid, s); break;
     }
   }
 }
 template <int PASS, int NP>
-void launch_np(int slot, const PcParams& p, const CUtensorMap& map, int grid, bool cor, IoType io, cudaStream_t s) {
-  if (io == IoType::f16) launch_slot<PASS, NP, false, __half>(slot, p, map, grid, s);
-  else if (cor) launch_slot<PASS, NP, true, float>(slot, p, map, grid, s);
-  else launch_slot<PASS, NP, false, float>(slot, p, map, grid, s);
+void launch_np(int slot, const PcParams& p, const CUtensorMap& map, const CUtensorMap& mapq, int grid, bool cor, IoType io, cudaStream_t s) {
+  if (io == IoType::f16) launch_slot<PASS, NP, false, __half>(slot, p, map, mapq, grid, s);
+  else if (cor) launch_slot<PASS, NP, true, float>(slot, p, map, mapq, grid, s);
+  else launch_slot<PASS, NP, false, float>(slot, p, map, mapq, grid, s);
 }
 // pass 1 (PASS = 1: pc_pass_kernel, whole-tile TMA box) or pass 2 (PASS = 2: pc_apply_kernel, 128 x 16 boxes)
 template <int PASS>
 void launch_pass(const PcCall& c, PcParams p, bool want_tma, cudaStream_t s) {
   const int np = c.L.np;
-  CUtensorMap map;
+  CUtensorMap map, mapq;
   memset(&map, 0, sizeof(map));
+  memset(&mapq, 0, sizeof(mapq));
   p.use_tma = (want_tma && tma_enabled() && make_tile_map(&map, c.A, c.lda, c.M, c.n, np, c.io, PASS == 2 ? 16 : 0)) ? 1 : 0;
+  p.use_tma_q = (PASS == 2 && want_tma && tma_enabled() && make_tile_map(&mapq, c.Q, c.ldq, c.M, c.n, np, c.io)) ? 1 : 0;
   int grid = c.L.grid;
-  if (PASS == 2) {   // one CTA of four tile pipelines per SM
+  if (PASS == 2) {   // one CTA of kApWg tile pipelines per SM
     const int g = (int)std::min<long long>(device_sm_count(), c.L.tiles);
     p.tiles_per_cta = (int)((c.L.tiles + g - 1) / g);
     grid = (int)((c.L.tiles + p.tiles_per_cta - 1) / p.tiles_per_cta);
   }
   const int slot = img_acquire(c.ws + c.L.cimg, s);
   switch (np) {
-    case 16: launch_np<PASS, 16>(slot, p, map, grid, c.cor, c.io, s); break;
-    case 32: launch_np<PASS, 32>(slot, p, map, grid, c.cor, c.io, s); break;
-    default: launch_np<PASS, 64>(slot, p, map, grid, c.cor, c.io, s); break;
+    case 16: launch_np<PASS, 16>(slot, p, map, mapq, grid, c.cor, c.io, s); break;
+    case 32: launch_np<PASS, 32>(slot, p, map, mapq, grid, c.cor, c.io, s); break;
+    default: launch_np<PASS, 64>(slot, p, map, mapq, grid, c.cor, c.io, s); break;
   }
   img_release(slot, s);
 }
