@@ -297,13 +297,15 @@ def main():
         torch.cuda.synchronize()
 
         # single GPU, n <= 64: the public host-buffer call overlaps the slab transfers with the two passes
-        pipe = tq.HostPipeline(m, n, args.mode, nslabs=8) if (P == 1 and n <= 64 and not args.reorth and not args.e2e_sequential) else None
+        # n <= 64: the public host-buffer call overlaps the slab transfers with the two passes (row-sharded at P > 1:
+        # every rank pipelines its own shard, one all-gather of the slab R factors)
+        pipe = tq.HostPipeline(m, n, args.mode, nslabs=8) if (n <= 64 and not args.reorth and not args.e2e_sequential) else None
         if pipe is not None:
             r_host = torch.empty((n, n), dtype=torch.float32, pin_memory=True)
 
         def e2e_step():
             if pipe is not None:
-                pipe.run(a_host, q_host, r_host)
+                pipe.run(a_host, q_host, r_host, world_size=P, rank=rank)
                 return
             a.t().copy_(a_host, non_blocking=True)
             if P > 1:
@@ -330,7 +332,7 @@ def main():
         e2e = {"value": flops(m * P, n) / (ems * 1e-3) / 1e9, "unit": "GFLOP/s", "ms_per_step": ems,
                "steps": e2e_steps, "h2d_bytes_per_step": m * n * esz * P,
                "d2h_bytes_per_step": (m * n * esz + n * n * 4) * P,
-               "api": ("tsqr_gpu_b200.HostPipeline.run: 8 row slabs, H2D | reduce and build | D2H overlapped on copy streams"
+               "api": ("tsqr_gpu_b200.HostPipeline.run: 8 row slabs per GPU, H2D | reduce and build | D2H overlapped on copy streams"
                        if pipe is not None else "H2D, tsqr_gpu_b200.qr / dist.tsqr_sharded, D2H on one stream")}
 
     if rank == 0:
@@ -344,8 +346,8 @@ def main():
         # label -> (kernel, algorithmic bytes per launch): first pass reads A once, second pass reads it again
         # and writes Q; anything else a kernel moves is implementation traffic
         kernels = {
-            101: ("pc_pass_kernel<1> (Z = A R_pre^-1, Gram accumulation: read A once)", balg_reduce, "pc1"),
-            103: ("pc_pass_kernel<2> (Z again, Q = Z C: read A, write Q)", balg_build, "pc2"),
+            101: ("pc_gram_kernel (pass 1: Z = A R_pre^-1, Gram accumulation: read A once)", balg_reduce, "pc1"),
+            103: ("pc_apply_kernel (pass 2: Z again, Q = Z C: read A, write Q)", balg_build, "pc2"),
             0: (("cs_reduce_kernel" if tc else "ts_pass_kernel<REDUCE>") + " level 0 (R-reduce pass: read A once)", balg_reduce, "reduce"),
             1: (("tc_build_kernel" if tc else "ts_pass_kernel<BUILD>") + " level 0 (Q-build pass: read the slab, write Q)", balg_build, "build"),
         }

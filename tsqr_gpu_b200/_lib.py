@@ -6,7 +6,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtsqr_b200.so")
+# TSQR_B200_LIB: load another build of the same library (same-box A/B measurements of kernel variants)
+LIB_PATH = os.environ.get("TSQR_B200_LIB") or os.path.join(_HERE, "libtsqr_b200.so")
 
 _c = ctypes
 _sz = ctypes.c_size_t

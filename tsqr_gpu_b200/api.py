@@ -274,12 +274,15 @@ class HostPipeline:
         self.ev_out = [torch.cuda.Event() for _ in range(S)]
         self.ev_start, self.ev_done = torch.cuda.Event(), torch.cuda.Event()
 
-    def run(self, a_host, q_host, r_host):
+    def run(self, a_host, q_host, r_host, group=None, world_size=1, rank=0):
         """a_host, q_host: (n, m) pinned; r_host: (n, n) float32 pinned (receives R column-major).
         Asynchronous: everything is ordered after the current stream's work and the current stream
-        waits for the last copy; synchronise it before reading the host buffers."""
+        waits for the last copy; synchronise it before reading the host buffers.
+        world_size > 1: this rank's matrix is one row shard of a matrix spread over `world_size` ranks (same m and
+        slab count on every rank); the only exchange is one all-gather of the slab R factors (torch.distributed)."""
         from .dist import stack_r_factors
         n, cur = self.n, torch.cuda.current_stream()
+        S = len(self.bounds)
         self.ev_start.record(cur)
         self.h2d.wait_event(self.ev_start)
         self.d2h.wait_event(self.ev_start)
@@ -292,10 +295,17 @@ class HostPipeline:
             cur.wait_event(self.ev_in[s])
             r_s, _ = tsqr_reduce(self.a[lo:hi], self.mode, self.ws[s], q=self.q[lo:hi])
             rs.append(r_s.t())                                   # R_s^T row-major = R_s column-major storage
-        stacked = stack_r_factors(torch.stack(rs))
-        q_root, r = tsqr(stacked, "fp32_notc")
+        local = torch.stack(rs)                                  # (S, n, n)
+        if world_size > 1:
+            import torch.distributed as dist
+            flat = torch.empty((world_size * S * n, n), dtype=torch.float32, device=local.device)
+            dist.all_gather_into_tensor(flat, local.reshape(S * n, n).contiguous(), group=group)
+            local = flat.view(world_size * S, n, n)
+        stacked = stack_r_factors(local)
+        q_root, r = tsqr(stacked, "fp32_notc")                   # redundant on every rank: identical bits
         for s, (lo, hi) in enumerate(self.bounds):
-            tsqr_build(self.a[lo:hi], self.mode, self.ws[s], b=q_root[s * n:(s + 1) * n], q=self.q[lo:hi])
+            k = rank * S + s
+            tsqr_build(self.a[lo:hi], self.mode, self.ws[s], b=q_root[k * n:(k + 1) * n], q=self.q[lo:hi])
             self.ev_out[s].record(cur)
             self.d2h.wait_event(self.ev_out[s])
             _memcpy2d_async(q_host[:, lo:hi], self.q[lo:hi].t(), self.d2h)

@@ -1,16 +1,19 @@
 // Preconditioned-Cholesky TSQR for sm_100a (see pc_tsqr.h for the algorithm).
 //
-// Kernels (one CTA = 128 threads = one 128-row tile at a time, thread t = tile row t = TMEM lane t):
-//   pc_sample_kernel : h = 8 NP strided rows of A -> R_pre (Householder sweep in the (column, row-segment)
-//                      register layout of cs_reduce.cu, column norms / reflector dots by shuffles)
-//   pc_pass_kernel<1>: TMA tile -> registers; Z = A R_pre^-1 panel by panel: 16 x 16 diagonal solves on
-//                      CUDA cores (no cross-thread traffic: a row of Z depends on its own row of A only),
-//                      off-diagonal updates U += Z_p R[p, trail] on tcgen05 with the A operand READ FROM
-//                      TENSOR MEMORY (tcgen05.st by the row's thread, hi/lo split fused into the store) and
-//                      the R blocks as shared-memory B operands; G_tile = [Z_hi | Z_lo]^T Z_hi as one
-//                      M = 128 product on 128-byte-swizzled K-major operands; fp32 -> fp64 accumulation
-//   pc_finish_kernel : sum of the CTA partials, chol, certificate, R = R_z R_pre, C = R_z^-1 (fp64)
-//   pc_pass_kernel<2>: Z again, Q_tile = Z C on tcgen05 (A operand from tensor memory), Q stored
+// Kernels (a tile = 128 rows, thread t of a 128-thread tile pipeline = tile row t = TMEM lane t; a CTA = three
+// independent tile pipelines, one CTA per SM):
+//   pc_sample_kernel : h = 8 NP rows of A -> R_pre (Householder sweep in the (column, row-segment) register layout
+//                      of cs_reduce.cu, column norms / reflector dots by shuffles); writes the constant-memory image
+//   pc_gram_kernel   : pass 1. TMA (128-byte swizzle) lands the tile in the Gram-operand layout; Z = A R_pre^-1 panel
+//                      by panel: 16 x 16 diagonal solves on CUDA cores with packed FFMA2 (no cross-thread traffic:
+//                      a row of Z depends on its own row of A only), off-diagonal updates U += Z_p R[p, trail] on
+//                      tcgen05 with the A operand READ FROM TENSOR MEMORY (tcgen05.st by the row's thread, hi/lo
+//                      split fused into the store) and the R blocks as shared-memory B operands; the thread
+//                      overwrites its own elements of the landed tile with Z_hi / Z_lo; G_tile = [Z_hi | Z_lo]^T Z_hi
+//                      as one M = 128 product; fp32 -> fp64 accumulation per pipeline
+//   pc_finish_kernel : sum of the partials, chol, certificate, R = R_z R_pre, C = R_z^-1 (fp64)
+//   pc_apply_kernel  : pass 2. Z again (same code, same bits), Q += Z_p C[16p:16p+16, :] on tcgen05 panel by panel,
+//                      Q leaves through shared memory and one TMA store per tile
 // Replaces, for the tensor-core modes, reference src/tcqr32x16.cu:1373-1469 (leaf QR), src/tsqr.cu:1102-1172
 // (R tree) and src/tsqr.cu:143-1061 (backward products).
 #include <cuda.h>
@@ -45,6 +48,7 @@ struct PcParams {
 // LDS.128 per thread and tile they kept the shared-memory pipe 70 % busy and bounded both passes). The image is
 // written per call by a stream-ordered device-to-device copy; kImgSlots slots, guarded by events, keep calls on
 // different streams apart; the kernels are instantiated per slot so that the operands are immediate addresses.
+constexpr int kApTmemPerWg = 160;   // TMEM columns per tile pipeline, 144 used: U [0, 48), D or G [48, 112), Z hi [112, 128), Z lo [128, 144)
 constexpr int kImgInv = 64 * 16;
 constexpr int kImgFloats = kImgInv + 64;
 constexpr int kImgSlots = 3;
@@ -278,105 +282,99 @@ __host__ __device__ constexpr uint32_t rblk_off(int p) {   // byte offset of R b
   for (int q = 0; q < p; ++q) o += kb::bytes(16, NP - 16 * (q + 1));
   return o;
 }
-template <int NP, int PASS>
-struct PassSmem {
+// ======================================================================================= pass 1
+// G = Z^T Z, Z = A R_pre^-1, with THREE tiles in flight per SM (one CTA of 3 warp groups per SM, each an independent
+// 128-row tile pipeline that works panel by panel like pc_apply_kernel). The Gram operand of a tile -- Z_hi and Z_lo,
+// K-major with K = tile rows, 128-byte hardware swizzle: 64 KB -- is also the LANDING buffer of the tile: the TMA
+// (tensor map with SWIZZLE_128B, one box of 32 rows x NP columns per K block) drops the raw rows of A exactly where
+// the operand layout wants column c of rows [32 kb, 32 kb + 32), every thread reads its own row from there, solves it
+// panel by panel and overwrites ITS OWN elements with Z_hi (Z_lo goes to line NP + c). The next tile may land as
+// soon as the Gram product of this one has been read by the tensor core. U += Z_p R[p, trail] takes Z_p from tensor
+// memory as in pass 2. Per tile: 144 TMEM columns (U 48, G 64, Z_p 32), 64 KB of shared memory.
+constexpr int kGrWg = 3;
+template <int NP>
+struct GramSmem {
   static constexpr int NPAN = NP / 16;
-  static constexpr uint32_t oLand = 0;                                                  // 128 x NP io elements
-  static constexpr uint32_t oBig = 32768;                                               // Gram operand | C hi, C lo
-  static constexpr uint32_t kBig = PASS == 1 ? sw::bytes(128) : 2 * kb::bytes(NP, NP);
   static constexpr uint32_t kRblk = rblk_off<NP>(NPAN - 1);
-  static constexpr uint32_t oRblkHi = oBig + kBig;
+  static constexpr uint32_t oRblkHi = 0;
   static constexpr uint32_t oRblkLo = oRblkHi + kRblk;
-  static constexpr uint32_t oBar = oRblkLo + kRblk;                                     // 4 mbarriers, tmem slot
-  static constexpr uint32_t kBytes = oBar + 64;
+  static constexpr uint32_t oBar = oRblkLo + kRblk;          // per warp group: full, mma, big; then the tmem slot
+  static constexpr uint32_t kBarBytes = 128;
+  static constexpr uint32_t kOp = sw::bytes(128);             // 65536
+  static constexpr uint32_t oWg = (oBar + kBarBytes + 1023) / 1024 * 1024;
+  static constexpr uint32_t kBytes = oWg + kGrWg * kOp;
 };
 
-template <int NP, bool COR, typename TIo, int PASS, int SLOT>
-__global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const __grid_constant__ CUtensorMap tmapA) {
-  using Sm = PassSmem<NP, PASS>;
+template <int NP, bool COR, typename TIo, int SLOT>
+__global__ void __launch_bounds__(128 * kGrWg, 1) pc_gram_kernel(const PcParams P, const __grid_constant__ CUtensorMap tmapG) {
+  using Sm = GramSmem<NP>;
   constexpr int NPAN = NP / 16;
   extern __shared__ __align__(1024) char sm[];
-  if (PASS == 2 && *P.status != kPcOk) return;   // the Householder passes behind this launch do the work
-  const int t = threadIdx.x, warp = t >> 5;
-  TIo* land = reinterpret_cast<TIo*>(sm + Sm::oLand);
-  char* big = sm + Sm::oBig;
+  const int tid = threadIdx.x, wg = tid >> 7, t = tid & 127, warp = (tid >> 5) & 3;
   char* RbHi = sm + Sm::oRblkHi;
   char* RbLo = sm + Sm::oRblkLo;
   const float* ci = cimg<SLOT>();
-  uint64_t* bar_full = reinterpret_cast<uint64_t*>(sm + Sm::oBar);
-  uint64_t* bar_mma = bar_full + 1;
-  uint64_t* bar_big = bar_full + 2;
-  uint64_t* bar_empty = bar_full + 3;   // 128 arrivals: every row of the landing buffer has been read
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_full + 4);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + Sm::oBar) + wg * 3;
+  uint64_t* bar_full = bars;
+  uint64_t* bar_mma = bars + 1;
+  uint64_t* bar_big = bars + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + Sm::oBar + Sm::kBarBytes - 8);
+  char* op = sm + Sm::oWg + wg * Sm::kOp;
   const int n = P.n;
   const TIo* A = reinterpret_cast<const TIo*>(P.A);
-  TIo* Q = reinterpret_cast<TIo*>(P.Q);
-  const bool use_tma = P.use_tma != 0;
+  // Corrected modes: the raw tile lands IN the operand (swizzled, fp32 only) once the previous Gram product has been
+  // read. Uncorrected modes: the lo lines of the operand are unused -- 8 KB per K block -- and serve as a separate
+  // landing buffer (plain 128 x 16 panel boxes, fp32 or fp16: panel p behind K block p), so the next tile is
+  // requested as soon as this tile's raw values have been read and lands while this tile is being worked on.
+  constexpr bool kLandLo = !COR;
+  const bool use_tma = (P.use_tma != 0) && (kLandLo || sizeof(TIo) == 4);
 
   if ((smem_u32(sm) & 1023u) != 0) __trap();   // the swizzled operand needs 1024-byte aligned atoms
-  if (warp == 0) tmem_alloc<256>(tmem_slot);
+  if (tid < 32) tmem_alloc<512>(tmem_slot);
   if (t == 0) {
     mbar_init(bar_full, 1);
     mbar_init(bar_mma, 1);
     mbar_init(bar_big, 1);
-    mbar_init(bar_empty, 128);
     fence_mbar_init();
-    if (use_tma) tma_prefetch_desc(&tmapA);
+    if (use_tma && wg == 0) tma_prefetch_desc(&tmapG);
   }
-  // operand images of R_pre (and C)
-  for (int idx = t; idx < NP * NP; idx += 128) {
+  for (int idx = tid; idx < NP * NP; idx += 128 * kGrWg) {   // operand image of R_pre's off-diagonal blocks
     const int k = idx % NP, c = idx / NP;
-    const float v = P.Rpre[idx];
     const int pk = k >> 4, pc = c >> 4;
-    if (pc > pk) {
-      const uint32_t o = rblk_off<NP>(pk) + kb::off(k & 15, c - 16 * (pk + 1), 16);
-      tile_store<COR>(RbHi, RbLo, o, v);
-    }
-    if (PASS == 2) {
-      char* CHi = big; char* CLo = big + kb::bytes(NP, NP);
-      tile_store<COR>(CHi, CLo, kb::off(k, c, NP), P.C[idx]);
-    }
+    if (pc > pk) tile_store<COR>(RbHi, RbLo, rblk_off<NP>(pk) + kb::off(k & 15, c - 16 * (pk + 1), 16), P.Rpre[idx]);
   }
   fence_async_smem();
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t tm = *tmem_slot;
-  const uint32_t tmU = tm, tmZh = tm + 64, tmZl = tm + 128, tmD = tm + 192;   // D: Gram (pass 1) or Q (pass 2)
-
+  const uint32_t tm = *tmem_slot + (uint32_t)(kApTmemPerWg * wg);
+  const uint32_t tmU = tm, tmG = tm + 48, tmZh = tm + 112, tmZl = tm + 128;
+  // this warp group's tiles: every kGrWg-th tile of the CTA's range
   const int tile_beg = blockIdx.x * P.tiles_per_cta;
   const int tile_end = min(tile_beg + P.tiles_per_cta, P.tiles);
-  const int ntl = max(tile_end - tile_beg, 0);
-  constexpr uint32_t kTileBytes = 128u * NP * sizeof(TIo);
-  // pass 2 walks its tiles backwards: the rows this CTA read last in pass 1 are the likeliest to be in L2
-  auto tile_of = [&](int i) { return PASS == 1 ? tile_beg + i : tile_end - 1 - i; };
-  if (use_tma && t == 0 && ntl > 0) {
-    mbar_arrive_expect_tx(bar_full, kTileBytes);
-    tma_load_2d(land, &tmapA, bar_full, tile_of(0) * kPcTileRows, 0);
-  }
-  uint32_t ph_full = 0, ph_mma = 0, ph_big = 0, ph_empty = 0;
+  const int ntl_cta = max(tile_end - tile_beg, 0);
+  const int ntl = ntl_cta > wg ? (ntl_cta - wg + kGrWg - 1) / kGrWg : 0;
+  auto tile_of = [&](int i) { return tile_beg + wg + kGrWg * i; };
+  auto issue_tile = [&](int i) {
+    mbar_arrive_expect_tx(bar_full, 128u * NP * (uint32_t)sizeof(TIo));
+    if (kLandLo) {   // NPAN boxes of 128 rows x 16 columns behind the hi lines of K block p
+#pragma unroll
+      for (int p = 0; p < NPAN; ++p) tma_load_2d(op + p * sw::kBlock + 8192, &tmapG, bar_full, tile_of(i) * kPcTileRows, 16 * p);
+    } else {         // 4 boxes of 32 rows x NP columns: K block kb, lines [0, NP)
+#pragma unroll
+      for (int kb4 = 0; kb4 < 4; ++kb4) tma_load_2d(op + kb4 * sw::kBlock, &tmapG, bar_full, tile_of(i) * kPcTileRows + 32 * kb4, 0);
+    }
+  };
+  if (use_tma && t == 0 && ntl > 0) issue_tile(0);
+  uint32_t ph_full = 0, ph_mma = 0, ph_big = 0;
+  const uint64_t dRh = smem_desc(smem_u32(RbHi), 128, 512), dRl = smem_desc(smem_u32(RbLo), 128, 512);
   float acc[NP];
 #pragma unroll
   for (int j = 0; j < NP; ++j) acc[j] = 0.f;
-  bool pending = false, first_flush = true;
+  bool first_flush = true;
   const int glanes = (COR ? 2 : 1) * NP;
-  double* gp = P.Gpart + (size_t)blockIdx.x * NP * 128 + t;
-  auto drain = [&]() {   // G_tile (lane = operand row: Z_hi columns, then Z_lo columns) -> acc
-    mbar_wait(bar_big, ph_big);
-    ph_big ^= 1;
-    fence_after_sync();
-#pragma unroll
-    for (int c0 = 0; c0 < NP; c0 += 16) {
-      float g[16];
-      tmem_ld16(tmem_addr(tmD, warp, c0), g);
-#pragma unroll
-      for (int i = 0; i < 16; i += 2) {
-        const f32x2 d = addp2(pack2(acc[c0 + i], acc[c0 + i + 1]), pack2(g[i], g[i + 1]));
-        unpack2(d, acc[c0 + i], acc[c0 + i + 1]);
-      }
-    }
-  };
-  auto flush = [&]() {
+  double* gp = P.Gpart + ((size_t)blockIdx.x * kGrWg + wg) * NP * 128 + t;
+  auto flush = [&]() {   // fp32 sums of at most 16 tiles -> the warp group's fp64 partial
     if (t < glanes) {
 #pragma unroll
       for (int j = 0; j < NP; ++j) {
@@ -388,154 +386,122 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
     for (int j = 0; j < NP; ++j) acc[j] = 0.f;
     first_flush = false;
   };
+  auto drain = [&]() {   // accumulator (lane = operand line: Z_hi columns, then Z_lo columns) -> registers
+#pragma unroll
+    for (int c0 = 0; c0 < NP; c0 += 16) {
+      float g[16];
+      tmem_ld16(tmem_addr(tmG, warp, c0), g);
+#pragma unroll
+      for (int j = 0; j < 16; j += 2) {
+        const f32x2 d = addp2(pack2(acc[c0 + j], acc[c0 + j + 1]), pack2(g[j], g[j + 1]));
+        unpack2(d, acc[c0 + j], acc[c0 + j + 1]);
+      }
+    }
+  };
+  // this thread's row inside the operand: K block t / 32, 16-byte chunk (t % 32) / 4 (XOR-swizzled with line % 8)
+  char* myrow = op + (uint32_t)(t >> 5) * sw::kBlock + (uint32_t)((t & 3) << 2);
+  const uint32_t q = (uint32_t)((t & 31) >> 2);
+  auto stage = [&](int p, const float (&zh)[16], const float (&zl)[16]) {   // Z_hi at line c, Z_lo at line NP + c
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int c = 16 * p + i;
+      const uint32_t o = (uint32_t)c * 128u + ((q ^ (uint32_t)(c & 7)) << 4);
+      *reinterpret_cast<float*>(myrow + o) = zh[i];
+      if (COR) *reinterpret_cast<float*>(myrow + o + (uint32_t)NP * 128u) = zl[i];
+    }
+  };
+  auto issue_u = [&](int p) {   // thread 0: U[:, 16(p+1):] (+)= Z_p R[p, 16(p+1):], Z_p in tensor memory
+    fence_after_sync();
+    const int N = NP - 16 * (p + 1);
+    const uint32_t id = idesc_tf32(128, N, false, false, false);
+    const uint32_t d = tmU + 16 * p;
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk) {
+      const uint64_t dh = dRh + (uint64_t)((rblk_off<NP>(p) + kk * 256) >> 4), dl = dRl + (uint64_t)((rblk_off<NP>(p) + kk * 256) >> 4);
+      mma_tf32_ts(d, tmZh + 8 * kk, dh, id, p > 0 || kk > 0);
+      if (COR) {
+        mma_tf32_ts(d, tmZh + 8 * kk, dl, id, true);
+        mma_tf32_ts(d, tmZl + 8 * kk, dh, id, true);
+      }
+    }
+    mma_commit(bar_mma);
+  };
 
   for (int it = 0; it < ntl; ++it) {
     const int tile = tile_of(it);
     const long long row = (long long)tile * kPcTileRows + t;
     const bool valid = row < P.M;
-    float y[NP];
     if (use_tma) {
       mbar_wait(bar_full, ph_full);
       ph_full ^= 1;
-#pragma unroll
-      for (int c = 0; c < NP; ++c) y[c] = io_plain(land + c * 128 + t);
-      // Release the landing buffer. Measured on B200: neither bar.sync nor mbarrier.arrive waits for shared-memory
-      // loads that have been issued but whose data has not come back, and the next TMA (async proxy) write into
-      // the buffer overtakes them (the last columns of a tile read the next tile, once in ~30000 tiles). The
-      // cross-proxy fence (MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC in SASS) completes the loads before the release.
-      fence_async_smem();
-      mbar_arrive(bar_empty);
-      if (t == 0 && it + 1 < ntl) {
-        mbar_wait(bar_empty, ph_empty);
-        mbar_arrive_expect_tx(bar_full, kTileBytes);
-        tma_load_2d(land, &tmapA, bar_full, tile_of(it + 1) * kPcTileRows, 0);
-      }
-      ph_empty ^= 1;
-    } else {
-      const TIo* ap = A + row;
-#pragma unroll
-      for (int c = 0; c < NP; ++c) y[c] = (valid && c < n) ? io_plain(ap + (long long)c * P.lda) : 0.f;
-    }
-    if (PASS == 1 && pending) {   // the previous tile's Gram product: its operands and its accumulator are free after this
-      drain();
-      pending = false;
-      if ((it & 15) == 0) flush();
     }
 #pragma unroll
     for (int p = 0; p < NPAN; ++p) {
+      float y[16];
+      if (use_tma && kLandLo) {
+        const TIo* land = reinterpret_cast<const TIo*>(op + p * sw::kBlock + 8192);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) y[i] = io_plain(land + i * 128 + t);
+      } else if (use_tma) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int c = 16 * p + i;
+          y[i] = *reinterpret_cast<const float*>(myrow + (uint32_t)c * 128u + ((q ^ (uint32_t)(c & 7)) << 4));
+        }
+      } else {
+        const TIo* ap = A + row + (long long)(16 * p) * P.lda;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) y[i] = (valid && 16 * p + i < n) ? io_load(ap + (long long)i * P.lda) : 0.f;
+      }
       if (p > 0) {   // y_p -= sum_{q<p} Z_q R[q, p]
         mbar_wait(bar_mma, ph_mma);
         ph_mma ^= 1;
         fence_after_sync();
         float u[16];
-        tmem_ld16(tmem_addr(tmU, warp, 16 * p), u);
+        tmem_ld16(tmem_addr(tmU, warp, 16 * (p - 1)), u);
 #pragma unroll
         for (int i = 0; i < 16; i += 2) {
-          const f32x2 d = sub2(pack2(y[16 * p + i], y[16 * p + i + 1]), pack2(u[i], u[i + 1]));
-          unpack2(d, y[16 * p + i], y[16 * p + i + 1]);
+          const f32x2 d = sub2(pack2(y[i], y[i + 1]), pack2(u[i], u[i + 1]));
+          unpack2(d, y[i], y[i + 1]);
         }
       }
-      // z_p R_pp = y_p : forward substitution along the row (packed, constants as uniform-register operands)
-      solve_panel16(*reinterpret_cast<float(*)[16]>(&y[16 * p]), ci, p);
-      if (p < NPAN - 1 || PASS == 2) {   // Z_p -> tensor memory as the A operand of the products that follow
-        float zh[16], zl[16];
+      solve_panel16(y, ci, p);
+      float zh[16], zl[16];
 #pragma unroll
-        // rounded to tf32 in EVERY mode, exactly as pc_apply_kernel stores its operand: the two passes must compute
-        // bit-identical Z (a difference of 2^-11 between them is amplified by cond(R_pre) in Q = Z C)
-        for (int i = 0; i < 16; ++i) { zh[i] = to_tf32_rna(y[16 * p + i]); zl[i] = __fsub_rn(y[16 * p + i], zh[i]); }
-        tmem_st16(tmem_addr(tmZh, warp, 16 * p), zh);
-        if (COR) tmem_st16(tmem_addr(tmZl, warp, 16 * p), zl);
-        tmem_wait_st();
-      }
+      for (int i = 0; i < 16; ++i) { zh[i] = to_tf32_rna(y[i]); zl[i] = __fsub_rn(y[i], zh[i]); }
+      stage(p, zh, zl);
       if (p < NPAN - 1) {
+        tmem_st16(tmem_addr(tmZh, warp, 0), zh);
+        if (COR) tmem_st16(tmem_addr(tmZl, warp, 0), zl);
+        tmem_wait_st();
         fence_before_sync();
-        __syncthreads();
-        if (t == 0) {
-          fence_after_sync();
-          const int N = NP - 16 * (p + 1);
-          const uint32_t id = idesc_tf32(128, N, false, false, false);
-          const uint32_t bh = smem_u32(RbHi) + rblk_off<NP>(p), bl = smem_u32(RbLo) + rblk_off<NP>(p);
-          const uint32_t d = tmU + 16 * (p + 1);
-#pragma unroll
-          for (int kk = 0; kk < 2; ++kk) {
-            const uint64_t dh = smem_desc(bh + kk * 256, 128, 512), dl = smem_desc(bl + kk * 256, 128, 512);
-            mma_tf32_ts(d, tmZh + 16 * p + 8 * kk, dh, id, p > 0 || kk > 0);
-            if (COR) {
-              mma_tf32_ts(d, tmZh + 16 * p + 8 * kk, dl, id, true);
-              mma_tf32_ts(d, tmZl + 16 * p + 8 * kk, dh, id, true);
-            }
-          }
-          mma_commit(bar_mma);
-        }
-      }
-      if (PASS == 1) {   // Gram operand: column 16p+i of Z at operand line 16p+i (hi) and NP+16p+i (lo)
-        const uint32_t rowpart = (uint32_t)(t >> 5) * sw::kBlock + (uint32_t)((t & 3) << 2);
-        const uint32_t q = (uint32_t)((t & 31) >> 2);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const int c = 16 * p + i;
-          const float z = y[c];
-          const float h = to_tf32_rna(z);
-          *reinterpret_cast<float*>(big + rowpart + (uint32_t)c * 128u + ((q ^ (uint32_t)(c & 7)) << 4)) = h;
-          if (COR) *reinterpret_cast<float*>(big + rowpart + (uint32_t)(NP + c) * 128u + ((q ^ (uint32_t)(c & 7)) << 4)) = __fsub_rn(z, h);
-        }
+        named_bar_sync(1 + wg, 128);
+        if (t == 0) issue_u(p);
       }
     }
-    if (PASS == 1) {
-      fence_async_smem();
-      fence_before_sync();
-      __syncthreads();
-      if (t == 0) {
-        fence_after_sync();
-        sw::gram_issue(tmD, smem_u32(big), NP, 128);
-        mma_commit(bar_big);
-      }
-      pending = true;
-    } else {
-      fence_before_sync();
-      __syncthreads();
-      if (t == 0) {
-        fence_after_sync();
-        const uint32_t id = idesc_tf32(128, NP, false, false, false);
-        const uint32_t ch = smem_u32(big), cl = ch + kb::bytes(NP, NP);
-#pragma unroll
-        for (int kk = 0; kk < NP / 8; ++kk) {
-          const uint64_t dh = smem_desc(ch + kk * 256, 128, kb::sbo(NP)), dl = smem_desc(cl + kk * 256, 128, kb::sbo(NP));
-          mma_tf32_ts(tmD, tmZh + 8 * kk, dh, id, kk > 0);
-          if (COR) {
-            mma_tf32_ts(tmD, tmZh + 8 * kk, dl, id, true);
-            mma_tf32_ts(tmD, tmZl + 8 * kk, dh, id, true);
-          }
-        }
-        mma_commit(bar_big);
-      }
-      mbar_wait(bar_big, ph_big);
-      ph_big ^= 1;
+    // G_tile = [Z_hi | Z_lo]^T Z_hi: one M = 128 product over the 128 rows
+    fence_async_smem();
+    fence_before_sync();
+    named_bar_sync(1 + wg, 128);
+    if (t == 0) {
       fence_after_sync();
-      TIo* qp = Q + row;
-      const bool full = (n == NP) && ((long long)(tile + 1) * kPcTileRows <= P.M);
-#pragma unroll
-      for (int c0 = 0; c0 < NP; c0 += 16) {
-        float qv[16];
-        tmem_ld16(tmem_addr(tmD, warp, c0), qv);
-        if (full) {
-#pragma unroll
-          for (int i = 0; i < 16; ++i) io_store(qp + (long long)(c0 + i) * P.ldq, qv[i]);
-        } else {
-#pragma unroll
-          for (int i = 0; i < 16; ++i)
-            if (valid && c0 + i < n) io_store(qp + (long long)(c0 + i) * P.ldq, qv[i]);
-        }
-      }
+      sw::gram_issue(tmG, smem_u32(op), NP, 128);
+      mma_commit(bar_big);
+      // separate landing buffer: every thread has read its raw values (barrier above). The M = 128 product also
+      // reads the lo lines, as rows of the accumulator nobody looks at: what it finds there does not matter.
+      if (kLandLo && use_tma && it + 1 < ntl) issue_tile(it + 1);
     }
+    mbar_wait(bar_big, ph_big);   // the tensor core has read the operand: the next tile may land on it
+    ph_big ^= 1;
+    fence_after_sync();
+    if (!kLandLo && use_tma && t == 0 && it + 1 < ntl) issue_tile(it + 1);
+    drain();
+    if ((it & 15) == 15) flush();
   }
-  if (PASS == 1) {
-    if (pending) drain();
-    flush();   // CTAs without tiles write zeros: the finish kernel sums every slot
-  }
+  flush();   // warp groups without tiles write zeros: the finish kernel sums every slot
   fence_before_sync();
   __syncthreads();
-  if (warp == 0) tmem_dealloc<256>(tm);
+  if (tid < 32) tmem_dealloc<512>(*tmem_slot);
 }
 
 // ======================================================================================= pass 2
@@ -552,7 +518,6 @@ __global__ void __launch_bounds__(128, 2) pc_pass_kernel(const PcParams P, const
 //     stores per thread); when ldq does not allow a tensor map the threads store their rows themselves.
 constexpr int kApSlots = 3;
 constexpr int kApWg = 3;
-constexpr int kApTmemPerWg = 160;   // 144 used: U [0, 48), D [48, 112), Z hi [112, 128), Z lo [128, 144)
 template <int NP, typename TIo>
 struct ApplySmem {
   static constexpr int NPAN = NP / 16;
@@ -969,7 +934,8 @@ EncodeFn encode_fn() {
 }
 // 2-D map of a column-major M x n matrix: dimension 0 = rows (contiguous), dimension 1 = columns (stride lda);
 // box = 128 rows x NP columns, out-of-range rows and columns read as zero
-bool make_tile_map(CUtensorMap* map, const void* A, long long lda, long long M, int n, int np, IoType io, int box_cols = 0) {
+bool make_tile_map(CUtensorMap* map, const void* A, long long lda, long long M, int n, int np, IoType io, int box_cols = 0,
+                   int box_rows = 128, bool swizzle128 = false) {
   EncodeFn fn = encode_fn();
   const size_t es = io == IoType::f16 ? 2 : 4;
   if (!fn) return false;
@@ -977,11 +943,11 @@ bool make_tile_map(CUtensorMap* map, const void* A, long long lda, long long M, 
   if (M >= (1ll << 31)) return false;
   cuuint64_t gdim[2] = {(cuuint64_t)M, (cuuint64_t)n};
   cuuint64_t gstr[1] = {(cuuint64_t)lda * es};
-  cuuint32_t box[2] = {128u, (cuuint32_t)(box_cols > 0 ? box_cols : np)};
+  cuuint32_t box[2] = {(cuuint32_t)box_rows, (cuuint32_t)(box_cols > 0 ? box_cols : np)};
   cuuint32_t estr[2] = {1u, 1u};
   const CUresult r = fn(map, io == IoType::f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
                         const_cast<void*>(A), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                        swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;
 }
 
@@ -1036,10 +1002,10 @@ void img_release(int slot, cudaStream_t s) {
 
 template <int NP, bool COR, typename TIo, int SLOT>
 void launch_pass1_t(const PcParams& p, const CUtensorMap& map, const CUtensorMap&, int grid, cudaStream_t s) {
-  auto kern = pc_pass_kernel<NP, COR, TIo, 1, SLOT>;
+  auto kern = pc_gram_kernel<NP, COR, TIo, SLOT>;
   static std::once_flag once;
-  std::call_once(once, [&] { set_smem(kern, (int)PassSmem<NP, 1>::kBytes); });
-  kern<<<grid, 128, PassSmem<NP, 1>::kBytes, s>>>(p, map);
+  std::call_once(once, [&] { set_smem(kern, (int)GramSmem<NP>::kBytes); });
+  kern<<<grid, 128 * kGrWg, GramSmem<NP>::kBytes, s>>>(p, map);
   note_launch();
   TSQR_CUDA_CHECK(cudaGetLastError());
 }
@@ -1074,21 +1040,21 @@ void launch_np(int slot, const PcParams& p, const CUtensorMap& map, const CUtens
   else if (cor) launch_slot<PASS, NP, true, float>(slot, p, map, mapq, grid, s);
   else launch_slot<PASS, NP, false, float>(slot, p, map, mapq, grid, s);
 }
-// pass 1 (PASS = 1: pc_pass_kernel, whole-tile TMA box) or pass 2 (PASS = 2: pc_apply_kernel, 128 x 16 boxes)
+// pass 1 (PASS = 1: pc_gram_kernel, swizzled 32-row boxes) or pass 2 (PASS = 2: pc_apply_kernel, 128 x 16 boxes)
 template <int PASS>
 void launch_pass(const PcCall& c, PcParams p, bool want_tma, cudaStream_t s) {
   const int np = c.L.np;
   CUtensorMap map, mapq;
   memset(&map, 0, sizeof(map));
   memset(&mapq, 0, sizeof(mapq));
-  p.use_tma = (want_tma && tma_enabled() && make_tile_map(&map, c.A, c.lda, c.M, c.n, np, c.io, PASS == 2 ? 16 : 0)) ? 1 : 0;
+  // pass 1, corrected modes: boxes of 32 rows x NP columns in the 128-byte-swizzled operand layout (fp32 only);
+  // pass 1, uncorrected modes and pass 2: plain 128 x 16 panels
+  if (PASS == 1 && c.cor) p.use_tma = (want_tma && tma_enabled() && c.io == IoType::f32 && make_tile_map(&map, c.A, c.lda, c.M, c.n, np, c.io, np, 32, true)) ? 1 : 0;
+  else p.use_tma = (want_tma && tma_enabled() && make_tile_map(&map, c.A, c.lda, c.M, c.n, np, c.io, 16)) ? 1 : 0;
   p.use_tma_q = (PASS == 2 && want_tma && tma_enabled() && make_tile_map(&mapq, c.Q, c.ldq, c.M, c.n, np, c.io)) ? 1 : 0;
-  int grid = c.L.grid;
-  if (PASS == 2) {   // one CTA of kApWg tile pipelines per SM
-    const int g = (int)std::min<long long>(device_sm_count(), c.L.tiles);
-    p.tiles_per_cta = (int)((c.L.tiles + g - 1) / g);
-    grid = (int)((c.L.tiles + p.tiles_per_cta - 1) / p.tiles_per_cta);
-  }
+  // both passes: one CTA of three tile pipelines per SM
+  const int grid = c.L.grid;
+  p.tiles_per_cta = c.L.tiles_per_cta;
   const int slot = img_acquire(c.ws + c.L.cimg, s);
   switch (np) {
     case 16: launch_np<PASS, 16>(slot, p, map, mapq, grid, c.cor, c.io, s); break;
@@ -1116,7 +1082,7 @@ void launch_finish_t(const PcCall& c, cudaStream_t s) {
   std::call_once(once, [&] { set_smem(kern, bytes); });
   const int lanes = (c.cor ? 2 : 1) * NP;
   const int grid = ((lanes + 31) / 32) * NP;
-  kern<<<grid, kFinThreads, bytes, s>>>(reinterpret_cast<const double*>(c.ws + c.L.gpart), c.L.grid,
+  kern<<<grid, kFinThreads, bytes, s>>>(reinterpret_cast<const double*>(c.ws + c.L.gpart), c.L.parts,
                                          reinterpret_cast<double*>(c.ws + c.L.gsum), c.ws + c.L.rpre, c.n, c.cor ? 1 : 0,
                                          kPcMaxEst, c.ws + c.L.rout, c.ws + c.L.cmat, c.ws + c.L.rzinv,
                                          reinterpret_cast<int*>(c.ws + c.L.status));
@@ -1146,10 +1112,11 @@ PcLayout pc_layout(long long m, int n) {
   PcLayout L;
   L.np = tc_np(n);
   L.tiles = (m + kPcTileRows - 1) / kPcTileRows;
-  const long long want = 2ll * device_sm_count();
+  const long long want = device_sm_count();
   L.grid = (int)std::min<long long>(want, L.tiles);
   L.tiles_per_cta = (int)((L.tiles + L.grid - 1) / L.grid);
   L.grid = (int)((L.tiles + L.tiles_per_cta - 1) / L.tiles_per_cta);
+  L.parts = 3 * L.grid;                                                   // one fp64 partial per tile pipeline (kGrWg per CTA)
   const size_t np2 = (size_t)L.np * L.np;
   size_t off = 0;
   L.rpre = off; off = align64(off + np2);
@@ -1160,7 +1127,7 @@ PcLayout pc_layout(long long m, int n) {
   L.cimg = off; off = align64(off + kImgFloats);
   L.gsum = off; off = align64(off + 2 * (2 * np2));                       // doubles
   // sized for the largest grid any device of this process can ask for (the query may run before a device is chosen)
-  const size_t gmax = (size_t)std::max<long long>(L.grid, std::min<long long>(2 * 160, L.tiles));
+  const size_t gmax = (size_t)std::max<long long>(L.parts, 3 * std::min<long long>(160, L.tiles));
   L.gpart = off; off = align64(off + 2 * gmax * (size_t)L.np * 128);      // doubles
   L.total = off;
   return L;

@@ -28,7 +28,7 @@ inline int pc_sample_rows(int np) { return 8 * np; }
 
 // float offsets of the PC region inside the workspace (all 64-float aligned)
 struct PcLayout {
-  int np = 0, grid = 0;
+  int np = 0, grid = 0, parts = 0;   // CTAs of a pass (one per SM), fp64 Gram partials (3 per CTA)
   long long tiles = 0;
   int tiles_per_cta = 0;
   size_t rpre = 0;     // NP x NP fp32, ld NP
@@ -37,7 +37,7 @@ struct PcLayout {
   size_t cmat = 0;     // NP x NP fp32, ld NP: C of pass 2
   size_t rzinv = 0;    // NP x NP fp32, ld NP: R_z^-1
   size_t cimg = 0;     // staging copy of the constant-memory image of R_pre's diagonal blocks
-  size_t gpart = 0;    // [grid][NP][128] doubles
+  size_t gpart = 0;    // [parts][NP][128] doubles
   size_t gsum = 0;     // [2 NP][NP] doubles
   size_t total = 0;
 };
