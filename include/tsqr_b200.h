@@ -103,6 +103,24 @@ int tsqr_b200_pc_probe(int mode, const void* a, size_t lda, size_t m, size_t n, 
                        void* q, size_t ldq, double* gsum, int use_tma, void* workspace, size_t workspace_bytes,
                        void* stream);
 
+/* Validation metrics in fp64 ON THE DEVICE, any n <= m; element type of the matrices follows `mode`. `result` is one
+ * double in device memory, `workspace` at least tsqr_b200_validation_workspace_bytes(n) bytes of device memory.
+ *   orthogonality = |Q^T Q - I|_F / sqrt(n)   replaces mtk::validation::check_orthogonality16 (reference src/validation.cu:43-80)
+ *   residual      = |A - Q R|_F / |A|_F       replaces the residual of the reference's test driver (reference src/test.cu:146-165);
+ *                   only the upper triangle of r is read */
+size_t tsqr_b200_validation_workspace_bytes(size_t n);
+int tsqr_b200_orthogonality(int mode, const void* q, size_t ldq, size_t m, size_t n, double* result, void* workspace,
+                            size_t workspace_bytes, void* stream);
+int tsqr_b200_residual(int mode, const void* a, size_t lda, const void* q, size_t ldq, const void* r, size_t ldr, size_t m, size_t n,
+                       double* result, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Conditioned test matrix on the device: a (m x n float, n <= 64) = U diag(s) V^T with U, V orthogonal factors of this
+ * library's QR of counter-based normals (a pure function of `seed`) and s_k = cond^(-k/(n-1)). Replaces
+ * mtk::utils::latms (reference src/latms.cu:9-121; singular values of src/test_cond.cu:31-50) without cuRAND/cuSOLVER. */
+size_t tsqr_b200_latms_workspace_bytes(size_t m, size_t n);
+int tsqr_b200_latms(float* a, size_t lda, size_t m, size_t n, float cond, unsigned long long seed, void* workspace,
+                    size_t workspace_bytes, void* stream);
+
 /* TSQR of A (m x n, n <= 64) for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses
  * that forbid cudaMalloc). No counterpart in the reference.
  * Same result as tsqr_b200_tsqr, but the workspace is a file-scope static __device__ array of

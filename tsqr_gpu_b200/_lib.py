@@ -32,6 +32,11 @@ SIGNATURES = {
     "tsqr_b200_pc_status": (_c.c_int, [_c.c_int, _sz, _sz, _vp, _vp, _vp]),
     "tsqr_b200_pc_probe": (_c.c_int, [_c.c_int, _vp, _sz, _sz, _sz, _vp, _vp, _vp, _sz, _vp, _c.c_int, _vp, _sz, _vp]),
     "tsqr_b200_tsqr_static": (_c.c_int, [_c.c_int, _vp, _sz, _vp, _sz, _vp, _sz, _sz, _sz, _vp]),
+    "tsqr_b200_validation_workspace_bytes": (_sz, [_sz]),
+    "tsqr_b200_orthogonality": (_c.c_int, [_c.c_int, _vp, _sz, _sz, _sz, _vp, _vp, _sz, _vp]),
+    "tsqr_b200_residual": (_c.c_int, [_c.c_int, _vp, _sz, _vp, _sz, _vp, _sz, _sz, _sz, _vp, _vp, _sz, _vp]),
+    "tsqr_b200_latms_workspace_bytes": (_sz, [_sz, _sz]),
+    "tsqr_b200_latms": (_c.c_int, [_vp, _sz, _sz, _sz, _c.c_float, _c.c_ulonglong, _vp, _sz, _vp]),
     "tsqr_b200_selftest_mma": (_c.c_int, [_c.c_int, _c.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 

@@ -347,5 +347,34 @@ def pc_probe(a, mode, rpre, c, use_tma=True):
     return q, gsum
 
 
+def orthogonality(q, mode="fp32_notc"):
+    """|Q^T Q - I|_F / sqrt(n) in fp64 on the device (reference src/validation.cu:43-80). Returns a 0-d float64 tensor."""
+    m, n = q.shape
+    ldq = _check_colmajor(q, "q")
+    out = torch.zeros((), dtype=torch.float64, device=q.device)
+    ws = torch.empty(lib.tsqr_b200_validation_workspace_bytes(n), dtype=torch.uint8, device=q.device)
+    _raise(lib.tsqr_b200_orthogonality(_mode(mode), q.data_ptr(), ldq, m, n, out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()))
+    return out
+
+
+def residual(a, q, r, mode="fp32_notc"):
+    """|A - Q R|_F / |A|_F in fp64 on the device (reference src/test.cu:146-165). Returns a 0-d float64 tensor."""
+    m, n = a.shape
+    lda, ldq, ldr = _check_colmajor(a, "a"), _check_colmajor(q, "q"), _check_colmajor(r, "r")
+    out = torch.zeros((), dtype=torch.float64, device=a.device)
+    ws = torch.empty(lib.tsqr_b200_validation_workspace_bytes(n), dtype=torch.uint8, device=a.device)
+    _raise(lib.tsqr_b200_residual(_mode(mode), a.data_ptr(), lda, q.data_ptr(), ldq, r.data_ptr(), ldr, m, n, out.data_ptr(),
+                                  ws.data_ptr(), ws.numel(), _stream()))
+    return out
+
+
+def latms(m, n, cond, seed=0, device="cuda"):
+    """conditioned m x n float32 test matrix generated on the device (reference src/latms.cu:9-121), column-major"""
+    a = colmajor_empty(m, n, torch.float32, device)
+    ws = torch.empty(lib.tsqr_b200_latms_workspace_bytes(m, n), dtype=torch.uint8, device=device)
+    _raise(lib.tsqr_b200_latms(a.data_ptr(), m, m, n, float(cond), int(seed), ws.data_ptr(), ws.numel(), _stream()))
+    return a
+
+
 def launch_count():
     return int(lib.tsqr_b200_launch_count())

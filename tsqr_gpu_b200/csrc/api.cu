@@ -166,6 +166,45 @@ int tsqr_b200_pc_status(int mode, size_t m, size_t n, const void* ws, void* stre
   });
 }
 
+size_t tsqr_b200_validation_workspace_bytes(size_t n) { return validation_workspace_bytes(n); }
+
+int tsqr_b200_orthogonality(int mode, const void* q, size_t ldq, size_t m, size_t n, double* result, void* ws, size_t ws_bytes,
+                            void* stream) {
+  if (!mode_valid(mode)) { set_err("invalid compute mode"); return TSQR_B200_ERR_ARGUMENT; }
+  if (m == 0 || n == 0 || n > m) return TSQR_B200_INVALID_SIZE;
+  if (!q || !result || !ws || ws_bytes < validation_workspace_bytes(n)) { set_err("null pointer or workspace too small"); return TSQR_B200_ERR_ARGUMENT; }
+  return guarded([&] {
+    orthogonality(mode_io(mode), q, (long long)ldq, (long long)m, (int)n, result, ws, (cudaStream_t)stream);
+    return 0;
+  });
+}
+
+int tsqr_b200_residual(int mode, const void* a, size_t lda, const void* q, size_t ldq, const void* r, size_t ldr, size_t m, size_t n,
+                       double* result, void* ws, size_t ws_bytes, void* stream) {
+  if (!mode_valid(mode)) { set_err("invalid compute mode"); return TSQR_B200_ERR_ARGUMENT; }
+  if (m == 0 || n == 0 || n > m) return TSQR_B200_INVALID_SIZE;
+  if (!a || !q || !r || !result || !ws || ws_bytes < 64) { set_err("null pointer or workspace too small"); return TSQR_B200_ERR_ARGUMENT; }
+  return guarded([&] {
+    residual(mode_io(mode), a, (long long)lda, q, (long long)ldq, r, (long long)ldr, (long long)m, (int)n, result, ws, (cudaStream_t)stream);
+    return 0;
+  });
+}
+
+size_t tsqr_b200_latms_workspace_bytes(size_t m, size_t n) {
+  if (m == 0 || n == 0 || n > 64 || n > m) return 256;
+  return latms_workspace_bytes((long long)m, (int)n);
+}
+
+int tsqr_b200_latms(float* a, size_t lda, size_t m, size_t n, float cond, unsigned long long seed, void* ws, size_t ws_bytes,
+                    void* stream) {
+  if (m == 0 || n == 0 || n > 64 || n > m) return TSQR_B200_INVALID_SIZE;
+  if (!a || !ws) { set_err("null pointer argument"); return TSQR_B200_ERR_ARGUMENT; }
+  return guarded([&] {
+    latms(a, (long long)lda, (long long)m, (int)n, cond, seed, (float*)ws, ws_bytes, (cudaStream_t)stream);
+    return 0;
+  });
+}
+
 int tsqr_b200_qr32x16_batched(int mode, void* q, size_t ldq, void* r, size_t ldr, const void* a, size_t lda,
                               unsigned m, unsigned n, size_t batch, const unsigned* starts, void* stream) {
   if (!mode_valid(mode)) { set_err("invalid compute mode"); return TSQR_B200_ERR_ARGUMENT; }

@@ -95,4 +95,13 @@ size_t qr_workspace_bytes(long long m, long long n, bool reorth);
 int qr_full(int mode, bool reorth, void* q, long long ldq, void* r, long long ldr, void* a, long long lda,
             long long m, long long n, float* ws, size_t ws_bytes, cudaStream_t s);
 
+// fp64 validation metrics on the device (validate.cu); `out` is one double in device memory
+size_t validation_workspace_bytes(size_t n);
+void orthogonality(IoType io, const void* q, long long ldq, long long m, int n, double* out, void* ws, cudaStream_t s);
+void residual(IoType io, const void* a, long long lda, const void* q, long long ldq, const void* r, long long ldr, long long m, int n,
+              double* out, void* ws, cudaStream_t s);
+// conditioned test matrices on the device (latms.cu)
+size_t latms_workspace_bytes(long long m, int n);
+void latms(float* a, long long lda, long long m, int n, float cond, unsigned long long seed, float* ws, size_t ws_bytes, cudaStream_t s);
+
 }  // namespace tsqr_b200
