@@ -50,7 +50,8 @@ def config_of(args, P):
     return {"workload": f"TSQR M=2^{args.m_log2} per GPU x N={n} {args.mode} "
                         f"(mtk::qr::qr<{args.mode},{str(args.reorth).lower()}>), column-major, uniform(-1,1) generated on device",
             "m_per_gpu": m, "m_total": m * P, "n": n, "mode": args.mode,
-            "parallelism": f"row-sharded x{P}, one all-gather of the {n}x{n} R factors" if P > 1 else "single GPU",
+            "parallelism": (f"row-sharded x{P}: tsqr_b200_tsqr_sharded, NCCL inside the library (broadcast of the {n}x{n} preconditioner + "
+                            f"all-reduce of the fp64 Gram sums)") if P > 1 else "single GPU",
             "l2": f"inputs ({m * n * esz / 2**30:.1f} GiB per GPU) are larger than the 126 MB L2; no flush needed"}
 
 
@@ -210,7 +211,7 @@ def main():
     import torch.distributed as dist
     import tsqr_gpu_b200 as tq
     from tsqr_gpu_b200._lib import lib
-    from tsqr_gpu_b200.dist import tsqr_sharded
+    from tsqr_gpu_b200.dist import ShardedTSQR
 
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
     torch.cuda.set_device(local_rank)
@@ -226,9 +227,11 @@ def main():
     r = torch.zeros((n, n), dtype=dt, device="cuda").t()
     buf = tq.Buffer().allocate(m, n, True)
 
+    sharded = ShardedTSQR() if P > 1 else None     # the library's own row-sharded driver (NCCL inside libtsqr_b200.so)
+
     def step():
         if P > 1:
-            return tsqr_sharded(a, args.mode, buf.ws, q=q, world_size=P, rank=rank)
+            return sharded.tsqr(a, args.mode, q=q, r=r)
         if a_pristine is not None:
             a.copy_(a_pristine)
         return tq.qr(a, args.mode, args.reorth, buf, q, r)
@@ -287,6 +290,36 @@ def main():
         orth_probe = float((g - torch.eye(n, device="cuda", dtype=torch.float64)).norm() / n ** 0.5)
         del g, qt
 
+    # ---- BASELINE config C4 (strong scaling): M = 2^26 rows in total, row-sharded over the P GPUs of this run
+    c4 = None
+    if P > 1 and n <= 64 and not args.reorth:
+        m4 = (1 << 26) // P
+        del q
+        a4 = make_input(m4, n, dt, 0x5EED0004 + rank)
+        q4 = tq.colmajor_empty(m4, n, dt)
+        r4 = torch.zeros((n, n), dtype=dt, device="cuda").t()
+        for _ in range(3):
+            sharded.tsqr(a4, args.mode, q=q4, r=r4)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        k4 = max(3, min(args.steps, 10))
+        g0.record()
+        for _ in range(k4):
+            sharded.tsqr(a4, args.mode, q=q4, r=r4)
+        g1.record()
+        barrier()
+        tt = torch.tensor([g0.elapsed_time(g1) / k4], device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms4 = float(tt.item())
+        balg4 = (3.0 * m4 * n + n * n) * esz
+        c4 = {"workload": f"C4: TSQR M=2^26 total x N={n} {args.mode}, row-sharded x{P} (strong scaling)", "m_total": 1 << 26,
+              "m_per_gpu": m4, "ms_per_step": ms4, "steps": k4, "gflops": flops(1 << 26, n) / (ms4 * 1e-3) / 1e9,
+              "hbm_gbs_per_gpu": balg4 / (ms4 * 1e-3) / 1e9}
+        del a4, q4
+        sharded._ws.pop((m4, n), None)
+        torch.cuda.empty_cache()
+        q = tq.colmajor_empty(m, n, dt)
+
     # ---- end-to-end through the public API with HOST buffers (H2D + D2H inside the timed region)
     e2e = None
     if not args.no_e2e:
@@ -309,7 +342,7 @@ def main():
                 return
             a.t().copy_(a_host, non_blocking=True)
             if P > 1:
-                _, rr = tsqr_sharded(a, args.mode, buf.ws, q=q, world_size=P, rank=rank)
+                _, rr = sharded.tsqr(a, args.mode, q=q, r=r)
             else:
                 _, rr = tq.qr(a, args.mode, args.reorth, buf, q, r)
             q_host.copy_(q.t(), non_blocking=True)
@@ -333,7 +366,7 @@ def main():
                "steps": e2e_steps, "h2d_bytes_per_step": m * n * esz * P,
                "d2h_bytes_per_step": (m * n * esz + n * n * 4) * P,
                "api": ("tsqr_gpu_b200.HostPipeline.run: 8 row slabs per GPU, H2D | reduce and build | D2H overlapped on copy streams"
-                       if pipe is not None else "H2D, tsqr_gpu_b200.qr / dist.tsqr_sharded, D2H on one stream")}
+                       if pipe is not None else "H2D, tsqr_gpu_b200.qr / dist.ShardedTSQR.tsqr, D2H on one stream")}
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -381,6 +414,9 @@ def main():
             "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e,
             "orthogonality_probe": orth_probe,
         }
+        if c4 is not None:
+            c4["hbm_frac_per_gpu"] = c4["hbm_gbs_per_gpu"] / peak
+            line["c4"] = c4
         if P == 1 and not args.no_cpu:
             try:
                 line["cpu_baseline"] = cpu_lapack_baseline(n)

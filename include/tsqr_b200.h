@@ -68,6 +68,24 @@ int tsqr_b200_tsqr_reduce(int mode, const void* a, size_t lda, size_t m, size_t 
 int tsqr_b200_tsqr_build(int mode, void* q, size_t ldq, const void* a, size_t lda, size_t m, size_t n,
                          const float* b, size_t ldb, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Row-sharded multi-GPU TSQR inside the library (one process or thread per GPU; NCCL on the caller's stream; the
+ * reference is single-GPU, this splits its tsqr16, reference src/tsqr.cu:1064-1279, across ranks). Rank p passes its
+ * own slab a (m_local x n, n <= 64) and receives its slab of Q and the full n x n R (identical on every rank).
+ *   tsqr_b200_nccl_unique_id : 128 bytes of ncclUniqueId, made on one rank and handed to the others by the caller
+ *   tsqr_b200_sharded_init   : collective; creates the communicator (current device = this rank's GPU); NULL on failure
+ *   tsqr_b200_sharded_attach : for callers that already own an ncclComm_t (passed as void*); not destroyed by _destroy
+ *   tsqr_b200_tsqr_sharded   : collective, every rank with the same mode and n. Tall slabs (>= 16384 rows on every rank)
+ *       in a *_tc_* mode: one ncclBroadcast of the 16 KB preconditioner + one ncclAllReduce of the 64 KB fp64 Gram
+ *       sums, no root factorisation; otherwise one ncclAllGather of the R factors + a redundant root factorisation.
+ *       Synchronises `stream` once per call (certificate read-back); NCCL is resolved at run time (libnccl.so.2). */
+int tsqr_b200_nccl_unique_id(void* out128);
+void* tsqr_b200_sharded_init(const void* id128, int nranks, int rank);
+void* tsqr_b200_sharded_attach(void* nccl_comm, int nranks, int rank);
+void tsqr_b200_sharded_destroy(void* handle);
+size_t tsqr_b200_sharded_workspace_bytes(size_t m_local, size_t n, int nranks);
+int tsqr_b200_tsqr_sharded(void* handle, int mode, void* q, size_t ldq, void* r, size_t ldr, const void* a, size_t lda,
+                           size_t m_local, size_t n, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Batched QR of small row blocks (<= 32 rows x <= 16 columns each). Replaces
  * mtk::tcqr::qr32x16_batched / qr32x16 (reference src/tcqr.hpp:22-37,
  * src/tcqr32x16.cu:1584-1634). q/a element type follows `mode`; r is float unless the

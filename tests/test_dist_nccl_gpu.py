@@ -22,3 +22,34 @@ def test_row_sharded_nccl(cuda):
            "--master-port", "29533", os.path.join(ROOT, "tests", "dist_nccl_check.py")]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert "DIST_OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
+
+
+def test_library_sharded_driver_single_rank(cuda, oracle):
+    """tsqr_b200_tsqr_sharded with a one-rank communicator (NCCL inside the library, no exchange partner): both forms
+    must reproduce the single-GPU entry point -- bit for bit in the preconditioned-Cholesky form (same stages)."""
+    import ctypes
+    import numpy as np
+    import tsqr_gpu_b200 as tq
+    from tsqr_gpu_b200._lib import lib
+    buf = ctypes.create_string_buffer(128)
+    assert lib.tsqr_b200_nccl_unique_id(buf) == 0, lib.tsqr_b200_last_error()
+    h = lib.tsqr_b200_sharded_init(buf.raw, 1, 0)
+    assert h, lib.tsqr_b200_last_error()
+    try:
+        for mode, m, n, exact in [("fp32_tc_cor", 1 << 17, 64, True), ("fp32_notc", 30000, 16, False), ("fp32_tc_cor", 5000, 48, False)]:
+            a = tq.to_colmajor(torch.from_numpy(oracle.uniform_matrix(m, n, seed=n)).cuda())
+            q = tq.colmajor_empty(m, n, torch.float32)
+            r = torch.zeros((n, n), device="cuda").t()
+            ws = torch.empty(lib.tsqr_b200_sharded_workspace_bytes(m, n, 1), dtype=torch.uint8, device="cuda")
+            code = lib.tsqr_b200_tsqr_sharded(h, tq.MODES[mode], q.data_ptr(), m, r.data_ptr(), n, a.data_ptr(), m, m, n,
+                                              ws.data_ptr(), ws.numel(), torch.cuda.current_stream().cuda_stream)
+            assert code == 0, lib.tsqr_b200_last_error()
+            q1, r1 = tq.tsqr(a, mode)
+            torch.cuda.synchronize()
+            if exact:
+                assert torch.equal(q, q1) and torch.equal(r, r1)
+            else:
+                q64, r64 = q.cpu().numpy().astype(np.float64), r.cpu().numpy().astype(np.float64)
+                assert oracle.orthogonality(q64) < 5e-6 and oracle.residual(q64, r64, a.cpu().numpy().astype(np.float64)) < 5e-6
+    finally:
+        lib.tsqr_b200_sharded_destroy(h)

@@ -202,15 +202,6 @@ def qr32x16_batched(a, starts, n, mode="fp32_notc"):
     return q, r
 
 
-def qr_host(a_host, q_host, r_host, a_dev, q_dev, r_dev, mode, reorthogonalize, buffer):
-    """End-to-end call with HOST buffers (pinned, column-major as (n, m) row-major arrays):
-    H2D of A, factorisation, D2H of Q and R, all on the current stream. Used for bench e2e."""
-    a_dev.t().copy_(a_host, non_blocking=True)
-    qr(a_dev, mode, reorthogonalize, buffer, q_dev, r_dev)
-    q_host.copy_(q_dev.t(), non_blocking=True)
-    r_host.copy_(r_dev.t(), non_blocking=True)
-
-
 _cudart = None
 
 

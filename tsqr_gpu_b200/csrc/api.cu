@@ -25,6 +25,8 @@ static void set_err(const char* msg) {
   g_err[sizeof(g_err) - 1] = 0;
 }
 
+void set_error_message(const char* msg) { set_err(msg); }
+
 // The reference takes its stream from the cuBLAS handle (src/blockqr.cu:58-59). cuBLAS is
 // not linked: cublasGetStream_v2 is looked up at run time, in the process first (the
 // caller that owns a handle has the library loaded), then by soname.

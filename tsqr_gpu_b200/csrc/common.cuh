@@ -28,6 +28,9 @@ __device__ __forceinline__ void io_store(__half* p, float v) { *p = __float2half
 
 constexpr unsigned kFullMask = 0xffffffffu;
 
+// message behind tsqr_b200_last_error() of the calling thread (api.cu)
+void set_error_message(const char* msg);
+
 // every kernel launch of the library is counted (reported by tsqr_b200_launch_count)
 void note_launch(unsigned n = 1);
 

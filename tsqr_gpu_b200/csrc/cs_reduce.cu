@@ -11,11 +11,10 @@
 //   * per column one RPT-term partial dot product per thread, one warp shuffle, an RS/2-warp combine
 //     through shared memory (the only block barrier of the step),
 //   * the Householder scalars (rsqrt / rcp), and the rank-1 update of the thread's columns.
-// Measured on B200: this right-looking, unblocked sweep needs fewer instructions per tile than
-// the blocked tcgen05 variant (tc_reduce_kernel, kept for comparison: TSQR_B200_REDUCE=tc) once
-// that one's operand conversions, TMEM round trips and single-thread MMA issue are counted, and
-// its 51 KB of shared memory allow 4 CTAs per SM instead of 2. The build pass (S = V^T V,
-// Q = -V X) stays on the tensor cores.
+// Its 51 KB of shared memory allow 4 CTAs per SM. The build pass (S = V^T V, Q = -V X) runs on the tensor cores.
+// (A blocked variant with the trailing update on tcgen05 was measured in round 1 -- 15.0 ms against 7.8 ms at 2^24 x 64,
+// profiles/r1_tc_reduce_full.* -- and removed in round 2, when the preconditioned-Cholesky passes of pc_tsqr.cu
+// became the fast path and this kernel its fallback.)
 // Replaces reference src/tcqr32x16.cu:1373-1469 (qr32x16_core with explicit H) and the R-tree
 // levels of src/tsqr.cu:1102-1172.
 #include <cstdlib>

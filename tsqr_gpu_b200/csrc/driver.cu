@@ -241,9 +241,7 @@ const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long ld
       if (rout && li + 1 == plan.levels.size()) { p.S = rout; p.lds = plan.n; }   // one home for R, whoever wrote it
       ProfScope prof(s, (int)li * 2);
       const IoType io = li == 0 ? mode_io(mode) : IoType::f32;
-      static const bool use_tc_reduce = [] { const char* e = std::getenv("TSQR_B200_REDUCE"); return e && e[0] == 't'; }();
-      if (use_tc_reduce) launch_tc_reduce(p, mode_is_cor(mode), io, io, s);
-      else launch_cs_reduce(p, io, io, s);
+      launch_cs_reduce(p, io, io, s);
     }
     return rout ? rout : ws + plan.levels.back().S_off;
   }

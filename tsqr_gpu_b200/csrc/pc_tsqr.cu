@@ -735,7 +735,9 @@ template <int NP>
 __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __restrict__ Gpart, int nparts, double* __restrict__ Gsum,
                                                                const float* __restrict__ Rpre, int n, int cor, float max_est,
                                                                float* __restrict__ Rout, float* __restrict__ Cmat,
-                                                               float* __restrict__ Rzinv, int* __restrict__ status) {
+                                                               float* __restrict__ Rzinv, int* __restrict__ status, int stage) {
+  // stage 0: sum the partials, the last CTA factors (single GPU); stage 1: sum only (the row-sharded driver all-reduces
+  // Gsum across the ranks next); stage 2: factor Gsum only (one CTA)
   extern __shared__ __align__(16) char smraw[];
   double* G = reinterpret_cast<double*>(smraw);         // [NP][NP] row-major: trailing matrix of the factorisation, then G^-1
   double* Rz = G + NP * NP;                              // R_z (upper)
@@ -745,7 +747,7 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
   __shared__ int s_last, s_bad;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int lanes = (cor ? 2 : 1) * NP;
-  {
+  if (stage != 2) {
     const int nlb = (lanes + 31) / 32;
     const int lb = blockIdx.x % nlb, j = blockIdx.x / nlb;
     const int l = 32 * lb + lane;
@@ -764,12 +766,15 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
       Gsum[l * NP + j] = r;
     }
   }
-  __threadfence();
-  __syncthreads();
-  if (t == 0) s_last = (atomicAdd(&status[1], 1) == (int)gridDim.x - 1);
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
+  if (stage == 1) return;
+  if (stage == 0) {
+    __threadfence();
+    __syncthreads();
+    if (t == 0) s_last = (atomicAdd(&status[1], 1) == (int)gridDim.x - 1);
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+  }
   const long long fclk0 = clock64();
   if (t == 0) s_bad = 0;
   // G = HH + LH + LH^T, symmetrised; padded columns get a unit diagonal
@@ -1075,17 +1080,17 @@ void launch_sample_t(const PcCall& c, cudaStream_t s) {
   TSQR_CUDA_CHECK(cudaGetLastError());
 }
 template <int NP>
-void launch_finish_t(const PcCall& c, cudaStream_t s) {
+void launch_finish_t(const PcCall& c, cudaStream_t s, int stage = 0) {
   auto kern = pc_finish_kernel<NP>;
   const int bytes = 4 * NP * NP * (int)sizeof(double);
   static std::once_flag once;
   std::call_once(once, [&] { set_smem(kern, bytes); });
   const int lanes = (c.cor ? 2 : 1) * NP;
-  const int grid = ((lanes + 31) / 32) * NP;
+  const int grid = stage == 2 ? 1 : ((lanes + 31) / 32) * NP;
   kern<<<grid, kFinThreads, bytes, s>>>(reinterpret_cast<const double*>(c.ws + c.L.gpart), c.L.parts,
                                          reinterpret_cast<double*>(c.ws + c.L.gsum), c.ws + c.L.rpre, c.n, c.cor ? 1 : 0,
                                          kPcMaxEst, c.ws + c.L.rout, c.ws + c.L.cmat, c.ws + c.L.rzinv,
-                                         reinterpret_cast<int*>(c.ws + c.L.status));
+                                         reinterpret_cast<int*>(c.ws + c.L.status), stage);
   note_launch();
   TSQR_CUDA_CHECK(cudaGetLastError());
 }
@@ -1155,7 +1160,34 @@ void pc_reduce(const PcCall& c, cudaStream_t s) {
 
 namespace {
 __global__ void pc_set_status_kernel(int* status, int v) { status[0] = v; }
+void finish_stage(const PcCall& c, cudaStream_t s, int stage) {
+  switch (c.L.np) {
+    case 16: launch_finish_t<16>(c, s, stage); break;
+    case 32: launch_finish_t<32>(c, s, stage); break;
+    default: launch_finish_t<64>(c, s, stage); break;
+  }
+}
 }  // namespace
+
+// ---- the stages one by one, for the row-sharded driver (sharded.cu): sample on one rank, R_pre broadcast, pass 1,
+// partial sums, all-reduce of Gsum, factorisation, pass 2
+void pc_stage_sample(const PcCall& c, cudaStream_t s) {
+  const int np = c.L.np;
+  if (c.io == IoType::f16) {
+    switch (np) { case 16: launch_sample_t<16, __half>(c, s); break; case 32: launch_sample_t<32, __half>(c, s); break; default: launch_sample_t<64, __half>(c, s); }
+  } else {
+    switch (np) { case 16: launch_sample_t<16, float>(c, s); break; case 32: launch_sample_t<32, float>(c, s); break; default: launch_sample_t<64, float>(c, s); }
+  }
+}
+void pc_stage_adopt_rpre(const PcCall& c, cudaStream_t s) {   // R_pre (in the workspace) came from elsewhere: image + status reset
+  TSQR_CUDA_CHECK(cudaMemsetAsync(c.ws + c.L.status, 0, 16 * sizeof(int), s));
+  pc_cimg_kernel<<<1, 256, 0, s>>>(c.ws + c.L.rpre, c.ws + c.L.cimg, c.L.np);
+  note_launch();
+  TSQR_CUDA_CHECK(cudaGetLastError());
+}
+void pc_stage_pass1(const PcCall& c, cudaStream_t s) { launch_pass<1>(c, pass_params(c), true, s); }
+void pc_stage_partial_sums(const PcCall& c, cudaStream_t s) { finish_stage(c, s, 1); }
+void pc_stage_factor(const PcCall& c, cudaStream_t s) { finish_stage(c, s, 2); }
 
 // pass 1 with a caller-supplied R_pre, then pass 2 with a caller-supplied C (tests of the operand layouts)
 void pc_probe(const PcCall& c, const float* rpre, const float* cmat, double* gsum_out, bool use_tma, cudaStream_t s) {

@@ -56,6 +56,14 @@ void pc_reduce(const PcCall& c, cudaStream_t s);
 // enqueue (C = R_z^-1 B) + pass 2; both return at once on the device unless status == kPcOk
 void pc_build(const PcCall& c, const float* B, long long ldb, cudaStream_t s);
 
+// the stages one by one (row-sharded driver): sample | adopt an R_pre written into ws + L.rpre by somebody else |
+// pass 1 | per-rank sums into ws + L.gsum ((2 NP) x NP doubles) | factor ws + L.gsum -> R, C, status. pc_build is pass 2.
+void pc_stage_sample(const PcCall& c, cudaStream_t s);
+void pc_stage_adopt_rpre(const PcCall& c, cudaStream_t s);
+void pc_stage_pass1(const PcCall& c, cudaStream_t s);
+void pc_stage_partial_sums(const PcCall& c, cudaStream_t s);
+void pc_stage_factor(const PcCall& c, cudaStream_t s);
+
 // tests: pass 1 with R_pre = rpre (gsum_out receives the 2 NP x NP fp64 sums: rows [0, NP) = Z_hi^T Z_hi,
 // rows [NP, 2 NP) = Z_lo^T Z_hi), then pass 2 with C = cmat. All pointers are device memory.
 void pc_probe(const PcCall& c, const float* rpre, const float* cmat, double* gsum_out, bool use_tma, cudaStream_t s);

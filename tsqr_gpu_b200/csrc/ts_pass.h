@@ -85,8 +85,7 @@ struct TcParams {
 constexpr int kPcOk = 0x600D;    // status word of the preconditioned-Cholesky path: certificate passed
 constexpr int kTcTileRows = 128;
 inline int tc_np(int n) { return n <= 16 ? 16 : (n <= 32 ? 32 : 64); }
-void launch_tc_reduce(const TcParams& p, bool corrected, IoType in, IoType q, cudaStream_t s);
-// default reduce pass of the tensor-core path: CUDA-core sweep in the (column, row-segment) layout
+// reduce pass of the Householder tensor-core path: CUDA-core sweep in the (column, row-segment) layout
 void launch_cs_reduce(const TcParams& p, IoType in, IoType q, cudaStream_t s);
 int cs_reduce_ctas_per_sm(int np);
 void launch_tc_build(const TcParams& p, bool corrected, IoType q, cudaStream_t s);

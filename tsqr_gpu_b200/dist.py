@@ -44,3 +44,51 @@ def tsqr_sharded(a_local, mode, ws, group=None, q=None, world_size=None, rank=No
     b = q_root[p * n:(p + 1) * n]                                    # column-major view, ld = P*n
     q = api.tsqr_build(a_local, mode, ws, b=b, q=q)
     return q, r
+
+
+class ShardedTSQR:
+    """ctypes mirror of the library's own row-sharded driver (tsqr_b200_tsqr_sharded, csrc/sharded.cu): the exchange is
+    done by NCCL inside the library on the current CUDA stream. torch.distributed is used once, to hand rank 0's
+    ncclUniqueId to the other ranks."""
+
+    def __init__(self, group=None):
+        import ctypes
+        from ._lib import lib
+        self.lib = lib
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        buf = ctypes.create_string_buffer(128)
+        if self.rank == 0 and lib.tsqr_b200_nccl_unique_id(buf) != 0:
+            raise RuntimeError(lib.tsqr_b200_last_error().decode())
+        dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+        t = torch.tensor(list(buf.raw), dtype=torch.uint8, device=dev)
+        dist.broadcast(t, src=0, group=group)
+        self._id = bytes(t.cpu().tolist())
+        self.handle = lib.tsqr_b200_sharded_init(self._id, self.world, self.rank)
+        if not self.handle:
+            raise RuntimeError("tsqr_b200_sharded_init failed: " + lib.tsqr_b200_last_error().decode())
+        self._ws = {}
+
+    def tsqr(self, a_local, mode, q=None, r=None):
+        from . import api
+        md = api._mode(mode)
+        m, n = a_local.shape
+        lda = api._check_colmajor(a_local, "a")
+        if q is None:
+            q = api.colmajor_empty(m, n, a_local.dtype, a_local.device)
+        if r is None:
+            r = torch.zeros((n, n), dtype=a_local.dtype, device=a_local.device).t()
+        key = (m, n)
+        if key not in self._ws:
+            self._ws[key] = torch.empty(self.lib.tsqr_b200_sharded_workspace_bytes(m, n, self.world), dtype=torch.uint8,
+                                        device=a_local.device)
+        ws = self._ws[key]
+        code = self.lib.tsqr_b200_tsqr_sharded(self.handle, md, q.data_ptr(), api._check_colmajor(q, "q"), r.data_ptr(),
+                                               api._check_colmajor(r, "r"), a_local.data_ptr(), lda, m, n, ws.data_ptr(),
+                                               ws.numel(), torch.cuda.current_stream().cuda_stream)
+        api._raise(code)
+        return q, r
+
+    def close(self):
+        if self.handle:
+            self.lib.tsqr_b200_sharded_destroy(self.handle)
+            self.handle = None
