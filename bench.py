@@ -392,6 +392,8 @@ def main():
         others = {names.get(lb, f"level{lb // 2}_{'build' if lb % 2 else 'reduce'}"): t for lb, t in sorted(t_lab.items())
                   if lb != dom_label}
         others["all_launches_total"] = t_all
+        if not dom["ms"] > 0.0:   # no labelled launch seen: say so instead of printing NaN
+            raise RuntimeError("bench.py: the timed region recorded no labelled pass launches (profile scopes missing on this path)")
         achieved = dom["bytes"] / (dom["ms"] * 1e-3) / 1e9
         traffic = None
         try:  # dram__bytes_read.sum + dram__bytes_write.sum of that kernel from the committed ncu capture

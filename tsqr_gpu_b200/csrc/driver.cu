@@ -247,6 +247,7 @@ const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long ld
   }
   for (size_t li = 0; li < plan.levels.size(); ++li) {
     PassParams p = level_params(plan, li, a, lda, ws);
+    p.emu = mode_emu(mode);
     ProfScope prof(s, (int)li * 2);
     launch_pass_simt(p, false, li == 0 ? mode_io(mode) : IoType::f32, IoType::f32, s);
   }
@@ -276,6 +277,7 @@ void tsqr_build(const Plan& plan, int mode, const void* a, long long lda, void* 
   for (size_t li = plan.levels.size(); li-- > 0;) {
     const Level& L = plan.levels[li];
     PassParams p = level_params(plan, li, a, lda, ws);
+    p.emu = mode_emu(mode);
     ProfScope prof(s, (int)li * 2 + 1);
     if (li + 1 == plan.levels.size()) {
       p.Bsrc = B;

@@ -58,6 +58,8 @@ int profile_read(int* labels, float* ms, int cap);  // returns #records copied, 
 Plan make_plan(long long m, int n, int max_chunks0 = 0, bool tc = false);
 // the *_tc_* modes run on the tensor-core passes when the matrix is tall enough
 inline bool mode_is_tc(int m) { return m == fp16_tc_nocor || m == fp32_tc_cor || m == fp32_tc_nocor || m == tf32_tc_cor || m == tf32_tc_nocor; }
+// operand rounding emulated by the CUDA-core passes in the three _emu modes (reference src/matmul.hpp:26-209)
+inline int mode_emu(int m) { return m == tf32_tc_nocor_emu ? 1 : (m == tf32_tc_cor_emu ? 2 : (m == mixed_tc_cor_emu ? 3 : 0)); }
 inline bool mode_is_cor(int m) { return m == fp32_tc_cor || m == tf32_tc_cor; }
 constexpr long long kTcMinRows = 1024;
 inline bool use_tc(int mode, long long m) { return mode_is_tc(mode) && m >= kTcMinRows; }

@@ -1173,6 +1173,7 @@ void finish_stage(const PcCall& c, cudaStream_t s, int stage) {
 // partial sums, all-reduce of Gsum, factorisation, pass 2
 void pc_stage_sample(const PcCall& c, cudaStream_t s) {
   const int np = c.L.np;
+  ProfScope prof(s, 100);
   if (c.io == IoType::f16) {
     switch (np) { case 16: launch_sample_t<16, __half>(c, s); break; case 32: launch_sample_t<32, __half>(c, s); break; default: launch_sample_t<64, __half>(c, s); }
   } else {
@@ -1185,9 +1186,18 @@ void pc_stage_adopt_rpre(const PcCall& c, cudaStream_t s) {   // R_pre (in the w
   note_launch();
   TSQR_CUDA_CHECK(cudaGetLastError());
 }
-void pc_stage_pass1(const PcCall& c, cudaStream_t s) { launch_pass<1>(c, pass_params(c), true, s); }
-void pc_stage_partial_sums(const PcCall& c, cudaStream_t s) { finish_stage(c, s, 1); }
-void pc_stage_factor(const PcCall& c, cudaStream_t s) { finish_stage(c, s, 2); }
+void pc_stage_pass1(const PcCall& c, cudaStream_t s) {
+  ProfScope prof(s, 101);
+  launch_pass<1>(c, pass_params(c), true, s);
+}
+void pc_stage_partial_sums(const PcCall& c, cudaStream_t s) {
+  ProfScope prof(s, 102);
+  finish_stage(c, s, 1);
+}
+void pc_stage_factor(const PcCall& c, cudaStream_t s) {
+  ProfScope prof(s, 102);
+  finish_stage(c, s, 2);
+}
 
 // pass 1 with a caller-supplied R_pre, then pass 2 with a caller-supplied C (tests of the operand layouts)
 void pc_probe(const PcCall& c, const float* rpre, const float* cmat, double* gsum_out, bool use_tma, cudaStream_t s) {

@@ -213,7 +213,10 @@ int tsqr_b200_tsqr_sharded(void* handle, int mode, void* q, size_t ldq, void* r,
       TSQR_CUDA_CHECK(cudaMemcpyAsync(sh->h_flag, c.ws + c.L.status, sizeof(int), cudaMemcpyDeviceToHost, s));
       TSQR_CUDA_CHECK(cudaStreamSynchronize(s));   // the certificate: identical on every rank (same Gram matrix)
       if (sh->h_flag[0] == kPcOk) {
-        pc_build(c, nullptr, 0, s);
+        {
+          ProfScope prof(s, 103);
+          pc_build(c, nullptr, 0, s);
+        }
         store_r(c.ws + c.L.rout, n, r, (long long)ldr, mode_io(mode), s);
         done = true;
       }
