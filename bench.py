@@ -332,11 +332,17 @@ def main():
         # single GPU, n <= 64: the public host-buffer call overlaps the slab transfers with the two passes
         # n <= 64: the public host-buffer call overlaps the slab transfers with the two passes (row-sharded at P > 1:
         # every rank pipelines its own shard, one all-gather of the slab R factors)
-        pipe = tq.HostPipeline(m, n, args.mode, nslabs=8) if (n <= 64 and not args.reorth and not args.e2e_sequential) else None
+        # (one GPU: the library's own C entry tsqr_b200_host_pipeline_run; row-sharded: the Python twin with its all-gather)
+        pipe = None
+        if n <= 64 and not args.reorth and not args.e2e_sequential:
+            pipe = tq.NativeHostPipeline(m, n, args.mode, nslabs=8) if P == 1 else tq.HostPipeline(m, n, args.mode, nslabs=8)
         if pipe is not None:
             r_host = torch.empty((n, n), dtype=torch.float32, pin_memory=True)
 
         def e2e_step():
+            if pipe is not None and P == 1:
+                pipe.run(a_host, q_host, r_host)
+                return
             if pipe is not None:
                 pipe.run(a_host, q_host, r_host, world_size=P, rank=rank)
                 return
@@ -365,7 +371,8 @@ def main():
         e2e = {"value": flops(m * P, n) / (ems * 1e-3) / 1e9, "unit": "GFLOP/s", "ms_per_step": ems,
                "steps": e2e_steps, "h2d_bytes_per_step": m * n * esz * P,
                "d2h_bytes_per_step": (m * n * esz + n * n * 4) * P,
-               "api": ("tsqr_gpu_b200.HostPipeline.run: 8 row slabs per GPU, H2D | reduce and build | D2H overlapped on copy streams"
+               "api": (("tsqr_b200_host_pipeline_run (C ABI, csrc/host_pipeline.cu)" if P == 1 else "tsqr_gpu_b200.HostPipeline.run")
+                       + ": 8 row slabs per GPU, H2D | reduce and build | D2H overlapped on copy streams"
                        if pipe is not None else "H2D, tsqr_gpu_b200.qr / dist.ShardedTSQR.tsqr, D2H on one stream")}
 
     if rank == 0:

@@ -86,6 +86,21 @@ size_t tsqr_b200_sharded_workspace_bytes(size_t m_local, size_t n, int nranks);
 int tsqr_b200_tsqr_sharded(void* handle, int mode, void* q, size_t ldq, void* r, size_t ldr, const void* a, size_t lda,
                            size_t m_local, size_t n, void* workspace, size_t workspace_bytes, void* stream);
 
+/* TSQR (n <= 64) of a matrix in HOST memory, overlapped with its own transfers (csrc/host_pipeline.cu). The reference's
+ * drivers stage the whole matrix with blocking copies around mtk::qr::qr (reference src/test.cu:118-127, :141-145); here
+ * the rows are cut into `nslabs` slabs, slab k is reduced while slab k+1 arrives and copied out while slab k+1 is built.
+ *   create : allocates the device copies of A and Q, the per-slab workspaces, two copy streams and the events on the
+ *            current device; NULL on failure (tsqr_b200_last_error)
+ *   run    : a_host, q_host column-major m x n of the mode's element type (lda, ldq >= m), r_host n x n float (ldr >= n,
+ *            the full R, zeros below the diagonal). Pinned host memory is needed for the overlap. Asynchronous: ordered
+ *            after `stream`'s work, and `stream` waits for the last copy -- synchronise it before reading the host
+ *            buffers. One run at a time per handle, on the device it was created on. */
+void* tsqr_b200_host_pipeline_create(int mode, size_t m, size_t n, int nslabs);
+int tsqr_b200_host_pipeline_slabs(void* handle);
+int tsqr_b200_host_pipeline_run(void* handle, const void* a_host, size_t lda, void* q_host, size_t ldq, float* r_host,
+                                size_t ldr, void* stream);
+void tsqr_b200_host_pipeline_destroy(void* handle);
+
 /* Batched QR of small row blocks (<= 32 rows x <= 16 columns each). Replaces
  * mtk::tcqr::qr32x16_batched / qr32x16 (reference src/tcqr.hpp:22-37,
  * src/tcqr32x16.cu:1584-1634). q/a element type follows `mode`; r is float unless the

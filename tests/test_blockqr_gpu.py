@@ -54,7 +54,7 @@ def test_blockqr_overwrites_a_only_when_wide(cuda, oracle):
 
 
 @pytest.mark.parametrize("mode", ["fp32_tc_cor", "tf32_tc_cor"])
-@pytest.mark.parametrize("m,n", [(4096, 128), (5000, 200), (2048, 65), (6000, 320)])
+@pytest.mark.parametrize("m,n", [(4096, 128), (5000, 200), (2048, 65), (6000, 320), (5001, 130)])
 @pytest.mark.parametrize("reorth", [False, True])
 def test_blockqr_tensor_core_modes(cuda, oracle, mode, m, n, reorth):
     """n > 64 in a *_tc_cor mode: TSQR panels and both projection GEMMs (tcgen05, hi/lo corrected)."""

@@ -2,7 +2,7 @@
 enp1s0/tsqr-gpu. The product is libtsqr_b200.so (C++/CUDA, C ABI in include/tsqr_b200.h);
 this package is the Python mirror of that interface used by the tests and bench.py."""
 from .api import (MODES, MODE_NAMES, Buffer, InvalidMatrixSize, colmajor_empty, io_dtype, launch_count, qr, tsqr,
-                  tsqr_build, tsqr_reduce, qr32x16_batched, to_colmajor, HostPipeline, pc_status, pc_probe, orthogonality, residual, latms)
+                  tsqr_build, tsqr_reduce, qr32x16_batched, to_colmajor, HostPipeline, NativeHostPipeline, pc_status, pc_probe, orthogonality, residual, latms)
 
 __all__ = ["MODES", "MODE_NAMES", "Buffer", "InvalidMatrixSize", "colmajor_empty", "io_dtype", "launch_count", "qr",
-           "tsqr", "tsqr_build", "tsqr_reduce", "qr32x16_batched", "to_colmajor", "HostPipeline", "pc_status", "pc_probe", "orthogonality", "residual", "latms"]
+           "tsqr", "tsqr_build", "tsqr_reduce", "qr32x16_batched", "to_colmajor", "HostPipeline", "NativeHostPipeline", "pc_status", "pc_probe", "orthogonality", "residual", "latms"]

@@ -38,6 +38,10 @@ SIGNATURES = {
     "tsqr_b200_latms_workspace_bytes": (_sz, [_sz, _sz]),
     "tsqr_b200_latms": (_c.c_int, [_vp, _sz, _sz, _sz, _c.c_float, _c.c_ulonglong, _vp, _sz, _vp]),
     "tsqr_b200_nccl_unique_id": (_c.c_int, [_vp]),
+    "tsqr_b200_host_pipeline_create": (_vp, [_c.c_int, _sz, _sz, _c.c_int]),
+    "tsqr_b200_host_pipeline_slabs": (_c.c_int, [_vp]),
+    "tsqr_b200_host_pipeline_run": (_c.c_int, [_vp, _vp, _sz, _vp, _sz, _vp, _sz, _vp]),
+    "tsqr_b200_host_pipeline_destroy": (None, [_vp]),
     "tsqr_b200_sharded_init": (_vp, [_vp, _c.c_int, _c.c_int]),
     "tsqr_b200_sharded_attach": (_vp, [_vp, _c.c_int, _c.c_int]),
     "tsqr_b200_sharded_destroy": (None, [_vp]),

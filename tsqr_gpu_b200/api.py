@@ -307,6 +307,41 @@ class HostPipeline:
         return r
 
 
+class NativeHostPipeline:
+    """The library's own host pipeline (tsqr_b200_host_pipeline_*, csrc/host_pipeline.cu): same slabbing and overlap as
+    HostPipeline, but device buffers, copy streams, events and the whole call sequence live in C++ behind the C ABI.
+    Host matrices are column-major, given as (n, m) row-major pinned tensors; r_host is (n, n) float32 and receives R
+    column-major (so r_host.t() is R)."""
+
+    def __init__(self, m, n, mode, nslabs=8):
+        self.m, self.n, self.mode = m, n, mode
+        self.dtype = io_dtype(mode)
+        if n > 64 or n > m or n < 1:
+            raise InvalidMatrixSize("NativeHostPipeline takes 0 < n <= 64, n <= m")
+        self.handle = lib.tsqr_b200_host_pipeline_create(_mode(mode), m, n, nslabs)
+        if not self.handle:
+            raise RuntimeError("tsqr_b200_host_pipeline_create failed: " + lib.tsqr_b200_last_error().decode())
+        self.nslabs = lib.tsqr_b200_host_pipeline_slabs(self.handle)
+
+    def run(self, a_host, q_host, r_host):
+        n, m = self.n, self.m
+        for name, t in (("a_host", a_host), ("q_host", q_host)):
+            if t.shape != (n, m) or t.dtype != self.dtype or t.stride(1) != 1 or t.is_cuda:
+                raise ValueError(f"{name}: need a host ({n}, {m}) {self.dtype} tensor with unit inner stride")
+        if r_host.shape != (n, n) or r_host.dtype != torch.float32 or r_host.stride(1) != 1 or r_host.is_cuda:
+            raise ValueError("r_host: need a host (n, n) float32 tensor with unit inner stride")
+        _raise(lib.tsqr_b200_host_pipeline_run(self.handle, a_host.data_ptr(), a_host.stride(0), q_host.data_ptr(), q_host.stride(0),
+                                               r_host.data_ptr(), r_host.stride(0), _stream()))
+
+    def close(self):
+        if getattr(self, "handle", None):
+            lib.tsqr_b200_host_pipeline_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        self.close()
+
+
 def pc_status(ws, m, n, mode):
     """Which path produced the last TSQR result held in workspace `ws` (a uint8 tensor, or a Buffer):
     (1, est) preconditioned-Cholesky fast path, (0, est) Householder fallback chosen on the device,

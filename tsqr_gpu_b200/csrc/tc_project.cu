@@ -16,6 +16,13 @@
 #include "driver.h"
 
 namespace tsqr_b200 {
+// tc_nn_tma.cu: the TMA-fed form of the update; false = not applicable, nothing launched
+bool launch_tc_nn_tma(bool corrected, IoType io, const void* X, long long ldx, int kb, const float* C, void* Y, long long ldy, int nb,
+                      long long M, cudaStream_t s);
+// tc_tn_tma.cu: the TMA-fed form of the coefficient product; returns the number of row ranges (2 partial slots each), 0 = not
+// applicable, nothing launched
+int launch_tc_tn_tma(bool corrected, IoType io, const void* X, long long ldx, int kb, const void* Y, long long ldy, int nb,
+                     long long M, int max_slabs, float* Cp, cudaStream_t s);
 namespace {
 using namespace tc;
 
@@ -228,13 +235,21 @@ void launch_typed(const T* X, long long ldx, int kb, T* Y, long long ldy, int nb
   auto nn = tc_nn_kernel<COR, T>;
   TSQR_CUDA_CHECK(cudaFuncSetAttribute(tn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTnSmem));
   TSQR_CUDA_CHECK(cudaFuncSetAttribute(nn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kNnSmem));
-  tn<<<nslabs, kT, kTnSmem, s>>>(X, ldx, kb, Y, ldy, nb, M, rows_per_slab, Cp);
-  note_launch();
-  reduce(Cp, 2 * nslabs, (size_t)kb * nb, C, s);
-  const int ngroups = (int)((M + 8 * kT - 1) / (8 * kT));
-  const int grid = std::min(ngroups, device_sm_count());
-  nn<<<grid, kT, kNnSmem, s>>>(X, ldx, kb, C, Y, ldy, nb, M, ngroups);
-  note_launch();
+  const IoType io = sizeof(T) == 2 ? IoType::f16 : IoType::f32;
+  const int ranges = launch_tc_tn_tma(COR, io, X, ldx, kb, Y, ldy, nb, M, nslabs, Cp, s);
+  if (ranges > 0) {
+    reduce(Cp, 2 * ranges, (size_t)kb * nb, C, s);
+  } else {
+    tn<<<nslabs, kT, kTnSmem, s>>>(X, ldx, kb, Y, ldy, nb, M, rows_per_slab, Cp);
+    note_launch();
+    reduce(Cp, 2 * nslabs, (size_t)kb * nb, C, s);
+  }
+  if (!launch_tc_nn_tma(COR, io, X, ldx, kb, C, Y, ldy, nb, M, s)) {
+    const int ngroups = (int)((M + 8 * kT - 1) / (8 * kT));
+    const int grid = std::min(ngroups, device_sm_count());
+    nn<<<grid, kT, kNnSmem, s>>>(X, ldx, kb, C, Y, ldy, nb, M, ngroups);
+    note_launch();
+  }
   TSQR_CUDA_CHECK(cudaGetLastError());
 }
 

@@ -1,0 +1,231 @@
+// BlockQR projection coefficients C = X^T Y on sm_100a as a TMA-fed streaming kernel (the first of the two GEMMs per
+// panel of reference src/blockqr.cu:92-116 / :272-291): X is m x kb (kb <= 512 per launch), Y is m x nb (nb <= 64).
+// HBM-bound: X and Y are read once. One CTA per SM walks a contiguous range of 64-row tiles:
+//   * TMA (cp.async.bulk.tensor) lands raw 64 x 64 blocks of Y and X in a 3-slot ring, decoupled from the compute;
+//   * 256 threads rewrite a landed block as the K-major tf32 operand (K = rows; 128-byte swizzle; hi in lines [0, 64),
+//     lo = x - hi in lines [64, 128) for the corrected modes) -- conflict-free thread-per-row stores;
+//   * D_b[128 x 64] += [X_b hi | X_b lo]^T Y hi (+ ... Y lo) with tcgen05.mma kind::tf32, one accumulator block of 64 TMEM
+//     columns per 64 columns of X, kept in tensor memory over the whole row range;
+//   * the two accumulator halves (hi^T Y, lo^T Y) leave as two partial slots per CTA, summed in fixed order by the caller.
+// tc_project.cu keeps the thread-staged kernel for matrices TMA cannot address.
+#include <cuda.h>
+#include <algorithm>
+#include <cstdlib>
+#include "common.cuh"
+#include "tc05.cuh"
+#include "driver.h"
+
+namespace tsqr_b200 {
+namespace {
+using namespace tc;
+
+constexpr int kThreads = 256;
+constexpr int kTile = 64;                       // rows per tile = 2 K blocks of the sw layout
+constexpr int kLand = 3;                        // landing slots
+constexpr uint32_t kOp = 2 * sw::kBlock;        // one 64-row operand buffer: 128 lines (hi | lo), 32 KB
+
+struct TnParams {
+  int kb, nb, nblk;
+  long long M;
+  int tiles, tiles_per_cta;
+  float* Cp;
+};
+
+template <typename TIo>
+struct TnSmem {
+  static constexpr uint32_t kSlot = (uint32_t)kTile * 64u * sizeof(TIo);   // raw block, [column][row]
+  static constexpr uint32_t oBar = 0;
+  static constexpr uint32_t oLand = 1024;
+  static constexpr uint32_t oX = (oLand + kLand * kSlot + 1023) / 1024 * 1024;
+  static constexpr uint32_t oY = oX + 2 * kOp;
+  static constexpr uint32_t kBytes = oY + 2 * kOp;
+};
+
+template <bool COR, typename TIo>
+__global__ void __launch_bounds__(kThreads, 1) tc_tn_tma_kernel(const TnParams P, const __grid_constant__ CUtensorMap tmapX,
+                                                                const __grid_constant__ CUtensorMap tmapY) {
+  using Sm = TnSmem<TIo>;
+  extern __shared__ __align__(1024) char sm[];
+  const int t = threadIdx.x, warp = t >> 5;
+  uint64_t* bar_full = reinterpret_cast<uint64_t*>(sm + Sm::oBar);
+  uint64_t* bar_empty = bar_full + kLand;
+  uint64_t* bar_mma = bar_empty + kLand;   // [2]: X operand stage of product q is q & 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + Sm::oBar + 128);
+  if (warp == 0) tmem_alloc<512>(tmem_slot);
+  if (t == 0) {
+    for (int i = 0; i < kLand; ++i) { mbar_init(bar_full + i, 1); mbar_init(bar_empty + i, kThreads); }
+    mbar_init(bar_mma, 1);
+    mbar_init(bar_mma + 1, 1);
+    fence_mbar_init();
+    tma_prefetch_desc(&tmapX);
+    tma_prefetch_desc(&tmapY);
+  }
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tm = *tmem_slot;
+  const int nblk = P.nblk, per = nblk + 1;   // items per tile: the Y block, then the X blocks
+  const int tile_beg = blockIdx.x * P.tiles_per_cta;
+  const int tile_end = min(tile_beg + P.tiles_per_cta, P.tiles);
+  const int ntl = max(tile_end - tile_beg, 0);
+  const int nitems = ntl * per;
+  auto issue_load = [&](int j) {   // item j -> landing slot j % kLand
+    const int slot = j % kLand, i = j / per, r = j % per;
+    mbar_arrive_expect_tx(bar_full + slot, Sm::kSlot);
+    if (r == 0) tma_load_2d(sm + Sm::oLand + slot * Sm::kSlot, &tmapY, bar_full + slot, (tile_beg + i) * kTile, 0);
+    else tma_load_2d(sm + Sm::oLand + slot * Sm::kSlot, &tmapX, bar_full + slot, (tile_beg + i) * kTile, 64 * (r - 1));
+  };
+  if (t == 0)
+    for (int j = 0; j < kLand && j < nitems; ++j) issue_load(j);
+
+  int nw = 0;   // products [0, nw) are known complete (commit q arrives on bar_mma[q & 1], parity (q >> 1) & 1)
+  auto wait_product = [&](int q) {
+    while (nw <= q) {
+      mbar_wait(bar_mma + (nw & 1), (uint32_t)(nw >> 1) & 1u);
+      ++nw;
+    }
+    fence_after_sync();
+  };
+  const int row = t & 63, cg = t >> 6;   // this thread converts columns [16 cg, 16 cg + 16) of row `row`
+  const uint32_t idesc = idesc_tf32(128, 64, false, false, false);
+
+  for (int j = 0; j < nitems; ++j) {
+    const int slot = j % kLand, i = j / per, r = j % per;
+    const int q = i * nblk + (r - 1);   // product index of an X item
+    char* op;
+    if (r == 0) {
+      if (i >= 2) wait_product((i - 1) * nblk - 1);   // every product of tile i - 2 read this Y buffer
+      op = sm + Sm::oY + (i & 1) * kOp;
+    } else {
+      if (q >= 2) wait_product(q - 2);                // the product that read this X buffer
+      op = sm + Sm::oX + (q & 1) * kOp;
+    }
+    mbar_wait(bar_full + slot, (uint32_t)(j / kLand) & 1u);
+    {
+      const TIo* land = reinterpret_cast<const TIo*>(sm + Sm::oLand + slot * Sm::kSlot);
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        const int col = 16 * cg + c;
+        const float x = io_plain(land + col * kTile + row);
+        const float h = to_tf32_rna(x);
+        *reinterpret_cast<float*>(op + sw::off(row, col)) = h;
+        if (COR) *reinterpret_cast<float*>(op + sw::off(row, 64 + col)) = __fsub_rn(x, h);
+      }
+    }
+    fence_async_smem();   // landing-slot reads before the next bulk write; operand stores before the tensor core reads them
+    mbar_arrive(bar_empty + slot);
+    if (t == 0 && j + kLand < nitems) {
+      mbar_wait(bar_empty + slot, (uint32_t)(j / kLand) & 1u);
+      issue_load(j + kLand);
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (r > 0 && t == 0) {
+      fence_after_sync();
+      const uint32_t xa = smem_u32(sm + Sm::oX + (q & 1) * kOp), ya = smem_u32(sm + Sm::oY + (i & 1) * kOp);
+      const uint32_t d = tm + 64u * (uint32_t)(r - 1);
+#pragma unroll
+      for (int kblk = 0; kblk < 2; ++kblk) {
+        const uint64_t da = smem_desc(xa + (uint32_t)kblk * sw::kBlock, 16, 1024, 2);
+        const uint64_t dh = smem_desc(ya + (uint32_t)kblk * sw::kBlock, 16, 1024, 2);
+        const uint64_t dl = smem_desc(ya + (uint32_t)kblk * sw::kBlock + 64u * 128u, 16, 1024, 2);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          mma_tf32(d, da + (uint64_t)(kk * 2), dh + (uint64_t)(kk * 2), idesc, i > 0 || kblk > 0 || kk > 0);
+          if (COR) mma_tf32(d, da + (uint64_t)(kk * 2), dl + (uint64_t)(kk * 2), idesc, true);
+        }
+      }
+      mma_commit(bar_mma + (q & 1));
+    }
+  }
+  if (ntl > 0) wait_product(ntl * nblk - 1);
+  // accumulator lane l < 64: row l of hi^T Y, lane 64 + l: row l of lo^T Y -> two partial slots; warps 0-3 take the even
+  // blocks, warps 4-7 the odd ones (a warp reaches the 32 TMEM lanes of its index modulo 4)
+  {
+    const int lane128 = (warp & 3) * 32 + (t & 31);
+    const int l = lane128 & 63, half = lane128 >> 6;
+    float* out = P.Cp + ((size_t)blockIdx.x * 2 + half) * (size_t)P.kb * P.nb;
+    const bool zero = ntl == 0 || (!COR && half == 1);
+    for (int b = warp >> 2; b < nblk; b += 2) {
+      const int irow = 64 * b + l;
+#pragma unroll
+      for (int c0 = 0; c0 < 64; c0 += 16) {
+        float v[16];
+        tmem_ld16(tmem_addr(tm + 64 * b, warp, c0), v);
+        if (irow < P.kb) {
+#pragma unroll
+          for (int e = 0; e < 16; ++e)
+            if (c0 + e < P.nb) out[irow + (size_t)(c0 + e) * P.kb] = zero ? 0.f : v[e];
+        }
+      }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<512>(tm);
+}
+
+using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                              const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                              CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeFn encode_fn() {
+  static EncodeFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess || qres != cudaDriverEntryPointSuccess) {
+      (void)cudaGetLastError();
+      p = nullptr;
+    }
+    return reinterpret_cast<EncodeFn>(p);
+  }();
+  return fn;
+}
+// column-major M x n matrix, box = 64 rows x 64 columns, rows and columns out of range read as zero
+bool block_map(CUtensorMap* map, const void* A, long long lda, long long M, int n, IoType io) {
+  EncodeFn fn = encode_fn();
+  const size_t es = io == IoType::f16 ? 2 : 4;
+  if (!fn || (reinterpret_cast<uintptr_t>(A) & 15u) != 0 || ((size_t)lda * es) % 16 != 0 || M >= (1ll << 31)) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)M, (cuuint64_t)n};
+  cuuint64_t gstr[1] = {(cuuint64_t)lda * es};
+  cuuint32_t box[2] = {(cuuint32_t)kTile, 64u};
+  cuuint32_t estr[2] = {1u, 1u};
+  return fn(map, io == IoType::f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(A), gdim,
+            gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <bool COR, typename TIo>
+int launch_t(IoType io, const void* X, long long ldx, int kb, const void* Y, long long ldy, int nb, long long M, int max_slabs,
+             float* Cp, cudaStream_t s) {
+  CUtensorMap mx, my;
+  if (!block_map(&mx, X, ldx, M, kb, io) || !block_map(&my, Y, ldy, M, nb, io)) return 0;
+  auto kern = tc_tn_tma_kernel<COR, TIo>;
+  TSQR_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TnSmem<TIo>::kBytes));
+  TnParams p{};
+  p.kb = kb; p.nb = nb; p.nblk = (kb + 63) / 64; p.M = M; p.Cp = Cp;
+  p.tiles = (int)((M + kTile - 1) / kTile);
+  int grid = std::min(std::min(device_sm_count(), p.tiles), max_slabs);
+  p.tiles_per_cta = (p.tiles + grid - 1) / grid;
+  grid = (p.tiles + p.tiles_per_cta - 1) / p.tiles_per_cta;   // no CTA without a tile
+  kern<<<grid, kThreads, TnSmem<TIo>::kBytes, s>>>(p, mx, my);
+  note_launch();
+  TSQR_CUDA_CHECK(cudaGetLastError());
+  return grid;
+}
+
+}  // namespace
+
+// Returns the number of row ranges (the caller sums 2 x that many partial slots of kb x nb floats in Cp), or 0 when
+// nothing was launched (TMA cannot address X or Y, kb > 512, or TSQR_B200_TMA=0): the caller runs its thread-staged kernel.
+int launch_tc_tn_tma(bool corrected, IoType io, const void* X, long long ldx, int kb, const void* Y, long long ldy, int nb,
+                     long long M, int max_slabs, float* Cp, cudaStream_t s) {
+  static const bool on = [] { const char* e = std::getenv("TSQR_B200_TMA"); return !(e && e[0] == '0'); }();
+  if (!on || kb < 1 || kb > 512 || max_slabs < 1) return 0;
+  if (io == IoType::f32)
+    return corrected ? launch_t<true, float>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, s)
+                     : launch_t<false, float>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, s);
+  return corrected ? launch_t<true, __half>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, s)
+                   : launch_t<false, __half>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, s);
+}
+
+}  // namespace tsqr_b200
