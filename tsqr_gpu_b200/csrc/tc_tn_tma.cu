@@ -2,7 +2,9 @@
 // panel of reference src/blockqr.cu:92-116 / :272-291): X is m x kb (kb <= 512 per launch), Y is m x nb (nb <= 64).
 // HBM-bound: X and Y are read once. One CTA per SM walks a contiguous range of 64-row tiles:
 //   * TMA (cp.async.bulk.tensor) lands raw 64 x 64 blocks of Y and X in a 3-slot ring, decoupled from the compute;
-//   * 256 threads rewrite a landed block as the K-major tf32 operand (K = rows; 128-byte swizzle; hi in lines [0, 64),
+//   * warp-specialised: one producer thread (TMA), one tensor-core issuer thread, 256 converter threads that only ever wait
+//     on mbarriers (no CTA-wide barrier in the loop);
+//   * the converter threads rewrite a landed block as the K-major tf32 operand (K = rows; 128-byte swizzle; hi in lines [0, 64),
 //     lo = x - hi in lines [64, 128) for the corrected modes) -- conflict-free thread-per-row stores;
 //   * D_b[128 x 64] += [X_b hi | X_b lo]^T Y hi (+ ... Y lo) with tcgen05.mma kind::tf32, one accumulator block of 64 TMEM
 //     columns per 64 columns of X, kept in tensor memory over the whole row range;
@@ -42,20 +44,21 @@ struct TnSmem {
 };
 
 template <bool COR, typename TIo>
-__global__ void __launch_bounds__(kThreads, 1) tc_tn_tma_kernel(const TnParams P, const __grid_constant__ CUtensorMap tmapX,
-                                                                const __grid_constant__ CUtensorMap tmapY) {
+__global__ void __launch_bounds__(kThreads + 64, 1) tc_tn_tma_kernel(const TnParams P, const __grid_constant__ CUtensorMap tmapX,
+                                                                     const __grid_constant__ CUtensorMap tmapY) {
   using Sm = TnSmem<TIo>;
   extern __shared__ __align__(1024) char sm[];
   const int t = threadIdx.x, warp = t >> 5;
-  uint64_t* bar_full = reinterpret_cast<uint64_t*>(sm + Sm::oBar);
-  uint64_t* bar_empty = bar_full + kLand;
-  uint64_t* bar_mma = bar_empty + kLand;   // [2]: X operand stage of product q is q & 1
+  uint64_t* bar_full = reinterpret_cast<uint64_t*>(sm + Sm::oBar);   // landing slot filled (TMA transaction bytes)
+  uint64_t* bar_empty = bar_full + kLand;                            // landing slot read by all converter threads
+  uint64_t* bar_mma = bar_empty + kLand;                             // [2] products that read X stage q & 1 are complete
+  uint64_t* bar_rx = bar_mma + 2;                                    // [2] X operand stage written by all converter threads
+  uint64_t* bar_ry = bar_rx + 2;                                     // [2] Y operand buffer written
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + Sm::oBar + 128);
   if (warp == 0) tmem_alloc<512>(tmem_slot);
   if (t == 0) {
     for (int i = 0; i < kLand; ++i) { mbar_init(bar_full + i, 1); mbar_init(bar_empty + i, kThreads); }
-    mbar_init(bar_mma, 1);
-    mbar_init(bar_mma + 1, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_mma + i, 1); mbar_init(bar_rx + i, kThreads); mbar_init(bar_ry + i, kThreads); }
     fence_mbar_init();
     tma_prefetch_desc(&tmapX);
     tma_prefetch_desc(&tmapY);
@@ -69,79 +72,90 @@ __global__ void __launch_bounds__(kThreads, 1) tc_tn_tma_kernel(const TnParams P
   const int tile_end = min(tile_beg + P.tiles_per_cta, P.tiles);
   const int ntl = max(tile_end - tile_beg, 0);
   const int nitems = ntl * per;
-  auto issue_load = [&](int j) {   // item j -> landing slot j % kLand
-    const int slot = j % kLand, i = j / per, r = j % per;
-    mbar_arrive_expect_tx(bar_full + slot, Sm::kSlot);
-    if (r == 0) tma_load_2d(sm + Sm::oLand + slot * Sm::kSlot, &tmapY, bar_full + slot, (tile_beg + i) * kTile, 0);
-    else tma_load_2d(sm + Sm::oLand + slot * Sm::kSlot, &tmapX, bar_full + slot, (tile_beg + i) * kTile, 64 * (r - 1));
-  };
-  if (t == 0)
-    for (int j = 0; j < kLand && j < nitems; ++j) issue_load(j);
 
-  int nw = 0;   // products [0, nw) are known complete (commit q arrives on bar_mma[q & 1], parity (q >> 1) & 1)
-  auto wait_product = [&](int q) {
-    while (nw <= q) {
-      mbar_wait(bar_mma + (nw & 1), (uint32_t)(nw >> 1) & 1u);
-      ++nw;
-    }
-    fence_after_sync();
-  };
-  const int row = t & 63, cg = t >> 6;   // this thread converts columns [16 cg, 16 cg + 16) of row `row`
-  const uint32_t idesc = idesc_tf32(128, 64, false, false, false);
-
-  for (int j = 0; j < nitems; ++j) {
-    const int slot = j % kLand, i = j / per, r = j % per;
-    const int q = i * nblk + (r - 1);   // product index of an X item
-    char* op;
-    if (r == 0) {
-      if (i >= 2) wait_product((i - 1) * nblk - 1);   // every product of tile i - 2 read this Y buffer
-      op = sm + Sm::oY + (i & 1) * kOp;
-    } else {
-      if (q >= 2) wait_product(q - 2);                // the product that read this X buffer
-      op = sm + Sm::oX + (q & 1) * kOp;
-    }
-    mbar_wait(bar_full + slot, (uint32_t)(j / kLand) & 1u);
-    {
-      const TIo* land = reinterpret_cast<const TIo*>(sm + Sm::oLand + slot * Sm::kSlot);
-#pragma unroll
-      for (int c = 0; c < 16; ++c) {
-        const int col = 16 * cg + c;
-        const float x = io_plain(land + col * kTile + row);
-        const float h = to_tf32_rna(x);
-        *reinterpret_cast<float*>(op + sw::off(row, col)) = h;
-        if (COR) *reinterpret_cast<float*>(op + sw::off(row, 64 + col)) = __fsub_rn(x, h);
+  if (warp == 9) {
+    // ---- producer: one thread keeps kLand block loads in flight
+    if (t == 9 * 32) {
+      for (int j = 0; j < nitems; ++j) {
+        const int slot = j % kLand, i = j / per, r = j % per;
+        if (j >= kLand) mbar_wait(bar_empty + slot, (uint32_t)(j / kLand - 1) & 1u);
+        mbar_arrive_expect_tx(bar_full + slot, Sm::kSlot);
+        if (r == 0) tma_load_2d(sm + Sm::oLand + slot * Sm::kSlot, &tmapY, bar_full + slot, (tile_beg + i) * kTile, 0);
+        else tma_load_2d(sm + Sm::oLand + slot * Sm::kSlot, &tmapX, bar_full + slot, (tile_beg + i) * kTile, 64 * (r - 1));
       }
     }
-    fence_async_smem();   // landing-slot reads before the next bulk write; operand stores before the tensor core reads them
-    mbar_arrive(bar_empty + slot);
-    if (t == 0 && j + kLand < nitems) {
-      mbar_wait(bar_empty + slot, (uint32_t)(j / kLand) & 1u);
-      issue_load(j + kLand);
-    }
-    fence_before_sync();
-    __syncthreads();
-    if (r > 0 && t == 0) {
-      fence_after_sync();
-      const uint32_t xa = smem_u32(sm + Sm::oX + (q & 1) * kOp), ya = smem_u32(sm + Sm::oY + (i & 1) * kOp);
-      const uint32_t d = tm + 64u * (uint32_t)(r - 1);
+  } else if (warp == 8) {
+    // ---- tensor-core issuer: one thread; product q reads X stage q & 1 and the Y buffer of its tile
+    if (t == 8 * 32) {
+      const uint32_t idesc = idesc_tf32(128, 64, false, false, false);
+      for (int i = 0; i < ntl; ++i) {
+        mbar_wait(bar_ry + (i & 1), (uint32_t)(i >> 1) & 1u);
+        const uint32_t ya = smem_u32(sm + Sm::oY + (i & 1) * kOp);
+        for (int b = 0; b < nblk; ++b) {
+          const int q = i * nblk + b;
+          mbar_wait(bar_rx + (q & 1), (uint32_t)(q >> 1) & 1u);
+          fence_after_sync();
+          const uint32_t xa = smem_u32(sm + Sm::oX + (q & 1) * kOp);
+          const uint32_t d = tm + 64u * (uint32_t)b;
 #pragma unroll
-      for (int kblk = 0; kblk < 2; ++kblk) {
-        const uint64_t da = smem_desc(xa + (uint32_t)kblk * sw::kBlock, 16, 1024, 2);
-        const uint64_t dh = smem_desc(ya + (uint32_t)kblk * sw::kBlock, 16, 1024, 2);
-        const uint64_t dl = smem_desc(ya + (uint32_t)kblk * sw::kBlock + 64u * 128u, 16, 1024, 2);
+          for (int kblk = 0; kblk < 2; ++kblk) {
+            const uint64_t da = smem_desc(xa + (uint32_t)kblk * sw::kBlock, 16, 1024, 2);
+            const uint64_t dh = smem_desc(ya + (uint32_t)kblk * sw::kBlock, 16, 1024, 2);
+            const uint64_t dl = smem_desc(ya + (uint32_t)kblk * sw::kBlock + 64u * 128u, 16, 1024, 2);
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-          mma_tf32(d, da + (uint64_t)(kk * 2), dh + (uint64_t)(kk * 2), idesc, i > 0 || kblk > 0 || kk > 0);
-          if (COR) mma_tf32(d, da + (uint64_t)(kk * 2), dl + (uint64_t)(kk * 2), idesc, true);
+            for (int kk = 0; kk < 4; ++kk) {
+              mma_tf32(d, da + (uint64_t)(kk * 2), dh + (uint64_t)(kk * 2), idesc, i > 0 || kblk > 0 || kk > 0);
+              if (COR) mma_tf32(d, da + (uint64_t)(kk * 2), dl + (uint64_t)(kk * 2), idesc, true);
+            }
+          }
+          mma_commit(bar_mma + (q & 1));
         }
       }
-      mma_commit(bar_mma + (q & 1));
     }
-  }
-  if (ntl > 0) wait_product(ntl * nblk - 1);
-  // accumulator lane l < 64: row l of hi^T Y, lane 64 + l: row l of lo^T Y -> two partial slots; warps 0-3 take the even
-  // blocks, warps 4-7 the odd ones (a warp reaches the 32 TMEM lanes of its index modulo 4)
-  {
+  } else {
+    // ---- converter threads: landed block -> K-major tf32 operand (hi, and lo for the corrected modes)
+    int nw = 0;   // products [0, nw) are known complete (commit q arrives on bar_mma[q & 1], parity (q >> 1) & 1)
+    auto wait_product = [&](int q) {
+      while (nw <= q) {
+        mbar_wait(bar_mma + (nw & 1), (uint32_t)(nw >> 1) & 1u);
+        ++nw;
+      }
+    };
+    const int row = t & 63, cg = t >> 6;   // this thread converts columns [16 cg, 16 cg + 16) of row `row`
+    uint32_t offs[8];                       // swizzled chunk of the row inside a 128-byte line, by line % 8
+#pragma unroll
+    for (int e = 0; e < 8; ++e) offs[e] = sw::off(row, e);
+    for (int j = 0; j < nitems; ++j) {
+      const int slot = j % kLand, i = j / per, r = j % per;
+      const int q = i * nblk + (r - 1);   // product index of an X item
+      char* op;
+      if (r == 0) {
+        if (i >= 2) wait_product((i - 1) * nblk - 1);   // every product of tile i - 2 read this Y buffer
+        op = sm + Sm::oY + (i & 1) * kOp;
+      } else {
+        if (q >= 2) wait_product(q - 2);                // the product that read this X stage
+        op = sm + Sm::oX + (q & 1) * kOp;
+      }
+      mbar_wait(bar_full + slot, (uint32_t)(j / kLand) & 1u);
+      {
+        const TIo* land = reinterpret_cast<const TIo*>(sm + Sm::oLand + slot * Sm::kSlot) + (16 * cg) * kTile + row;
+        char* dst = op + (16 * cg) * 128;
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+          const float x = io_plain(land + c * kTile);
+          const float h = to_tf32_rna(x);
+          *reinterpret_cast<float*>(dst + (c & ~7) * 128 + offs[c & 7]) = h;
+          if (COR) *reinterpret_cast<float*>(dst + 64 * 128 + (c & ~7) * 128 + offs[c & 7]) = __fsub_rn(x, h);
+        }
+      }
+      fence_async_smem();   // landing-slot reads before the next bulk write; operand stores before the tensor core reads them
+      mbar_arrive(bar_empty + slot);
+      mbar_arrive(r == 0 ? bar_ry + (i & 1) : bar_rx + (q & 1));
+    }
+    if (ntl > 0) wait_product(ntl * nblk - 1);
+    fence_after_sync();
+    // accumulator lane l < 64: row l of hi^T Y, lane 64 + l: row l of lo^T Y -> two partial slots; warps 0-3 take the
+    // even blocks, warps 4-7 the odd ones (a warp reaches the 32 TMEM lanes of its index modulo 4)
     const int lane128 = (warp & 3) * 32 + (t & 31);
     const int l = lane128 & 63, half = lane128 >> 6;
     float* out = P.Cp + ((size_t)blockIdx.x * 2 + half) * (size_t)P.kb * P.nb;
@@ -207,7 +221,7 @@ int launch_t(IoType io, const void* X, long long ldx, int kb, const void* Y, lon
   int grid = std::min(std::min(device_sm_count(), p.tiles), max_slabs);
   p.tiles_per_cta = (p.tiles + grid - 1) / grid;
   grid = (p.tiles + p.tiles_per_cta - 1) / p.tiles_per_cta;   // no CTA without a tile
-  kern<<<grid, kThreads, TnSmem<TIo>::kBytes, s>>>(p, mx, my);
+  kern<<<grid, kThreads + 64, TnSmem<TIo>::kBytes, s>>>(p, mx, my);
   note_launch();
   TSQR_CUDA_CHECK(cudaGetLastError());
   return grid;
