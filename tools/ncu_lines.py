@@ -71,6 +71,8 @@ def kern_sub_matches(ncu_name, mangled_sub):
     # mangled: tc_reduce_kernelILi64ELb1EffE / cs_reduce_kernelILi64ELi4EffE -> base name + first two template args
     base = re.search(r"([a-z]+_[a-z]+_kernel)", mangled_sub).group(1)
     m = re.search(r"ILi(\d+)EL([bi])(\d+)", mangled_sub)
+    if m is None:   # kernels without the <int, bool|int, ...> head: match on the base name only
+        return base in ncu_name
     second = f"(bool){m.group(3)}" if m.group(2) == "b" else f"(int){m.group(3)}"
     return base in ncu_name and f"(int){m.group(1)}, {second}" in ncu_name
 

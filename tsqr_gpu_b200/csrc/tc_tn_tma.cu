@@ -2,10 +2,11 @@
 // panel of reference src/blockqr.cu:92-116 / :272-291): X is m x kb (kb <= 512 per launch), Y is m x nb (nb <= 64).
 // HBM-bound: X and Y are read once. One CTA per SM walks a contiguous range of 64-row tiles:
 //   * TMA (cp.async.bulk.tensor) lands raw 64 x 64 blocks of Y and X in a 3-slot ring, decoupled from the compute;
-//   * warp-specialised: one producer thread (TMA), one tensor-core issuer thread, 256 converter threads that only ever wait
+//   * warp-specialised: one producer thread (TMA), one tensor-core issuer thread, 512 converter threads that only ever wait
 //     on mbarriers (no CTA-wide barrier in the loop);
 //   * the converter threads rewrite a landed block as the K-major tf32 operand (K = rows; 128-byte swizzle; hi in lines [0, 64),
-//     lo = x - hi in lines [64, 128) for the corrected modes) -- conflict-free thread-per-row stores;
+//     lo = x - hi in lines [64, 128) for the corrected modes) -- conflict-free thread-per-row stores; 16 warps so that the
+//     fence / barrier latencies of one warp hide behind the others;
 //   * D_b[128 x 64] += [X_b hi | X_b lo]^T Y hi (+ ... Y lo) with tcgen05.mma kind::tf32, one accumulator block of 64 TMEM
 //     columns per 64 columns of X, kept in tensor memory over the whole row range;
 //   * the two accumulator halves (hi^T Y, lo^T Y) leave as two partial slots per CTA, summed in fixed order by the caller.
@@ -21,7 +22,9 @@ namespace tsqr_b200 {
 namespace {
 using namespace tc;
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 512;                   // converter threads (16 warps); + 1 issuer warp + 1 producer warp
+constexpr int kConvWarps = kThreads / 32;
+constexpr int kColsPerThread = 64 * 64 / kThreads;   // 8
 constexpr int kTile = 64;                       // rows per tile = 2 K blocks of the sw layout
 constexpr int kLand = 3;                        // landing slots
 constexpr uint32_t kOp = 2 * sw::kBlock;        // one 64-row operand buffer: 128 lines (hi | lo), 32 KB
@@ -73,9 +76,9 @@ __global__ void __launch_bounds__(kThreads + 64, 1) tc_tn_tma_kernel(const TnPar
   const int ntl = max(tile_end - tile_beg, 0);
   const int nitems = ntl * per;
 
-  if (warp == 9) {
+  if (warp == kConvWarps + 1) {
     // ---- producer: one thread keeps kLand block loads in flight
-    if (t == 9 * 32) {
+    if (t == (kConvWarps + 1) * 32) {
       for (int j = 0; j < nitems; ++j) {
         const int slot = j % kLand, i = j / per, r = j % per;
         if (j >= kLand) mbar_wait(bar_empty + slot, (uint32_t)(j / kLand - 1) & 1u);
@@ -84,9 +87,9 @@ __global__ void __launch_bounds__(kThreads + 64, 1) tc_tn_tma_kernel(const TnPar
         else tma_load_2d(sm + Sm::oLand + slot * Sm::kSlot, &tmapX, bar_full + slot, (tile_beg + i) * kTile, 64 * (r - 1));
       }
     }
-  } else if (warp == 8) {
+  } else if (warp == kConvWarps) {
     // ---- tensor-core issuer: one thread; product q reads X stage q & 1 and the Y buffer of its tile
-    if (t == 8 * 32) {
+    if (t == kConvWarps * 32) {
       const uint32_t idesc = idesc_tf32(128, 64, false, false, false);
       for (int i = 0; i < ntl; ++i) {
         mbar_wait(bar_ry + (i & 1), (uint32_t)(i >> 1) & 1u);
@@ -121,7 +124,7 @@ __global__ void __launch_bounds__(kThreads + 64, 1) tc_tn_tma_kernel(const TnPar
         ++nw;
       }
     };
-    const int row = t & 63, cg = t >> 6;   // this thread converts columns [16 cg, 16 cg + 16) of row `row`
+    const int row = t & 63, cg = t >> 6;   // this thread converts columns [8 cg, 8 cg + 8) of row `row`
     uint32_t offs[8];                       // swizzled chunk of the row inside a 128-byte line, by line % 8
 #pragma unroll
     for (int e = 0; e < 8; ++e) offs[e] = sw::off(row, e);
@@ -138,10 +141,11 @@ __global__ void __launch_bounds__(kThreads + 64, 1) tc_tn_tma_kernel(const TnPar
       }
       mbar_wait(bar_full + slot, (uint32_t)(j / kLand) & 1u);
       {
-        const TIo* land = reinterpret_cast<const TIo*>(sm + Sm::oLand + slot * Sm::kSlot) + (16 * cg) * kTile + row;
-        char* dst = op + (16 * cg) * 128;
+        static_assert(kColsPerThread == 8, "one 8-line swizzle atom per thread");
+        const TIo* land = reinterpret_cast<const TIo*>(sm + Sm::oLand + slot * Sm::kSlot) + (kColsPerThread * cg) * kTile + row;
+        char* dst = op + (kColsPerThread * cg) * 128;
 #pragma unroll
-        for (int c = 0; c < 16; ++c) {
+        for (int c = 0; c < kColsPerThread; ++c) {
           const float x = io_plain(land + c * kTile);
           const float h = to_tf32_rna(x);
           *reinterpret_cast<float*>(dst + (c & ~7) * 128 + offs[c & 7]) = h;
@@ -154,13 +158,13 @@ __global__ void __launch_bounds__(kThreads + 64, 1) tc_tn_tma_kernel(const TnPar
     }
     if (ntl > 0) wait_product(ntl * nblk - 1);
     fence_after_sync();
-    // accumulator lane l < 64: row l of hi^T Y, lane 64 + l: row l of lo^T Y -> two partial slots; warps 0-3 take the
-    // even blocks, warps 4-7 the odd ones (a warp reaches the 32 TMEM lanes of its index modulo 4)
+    // accumulator lane l < 64: row l of hi^T Y, lane 64 + l: row l of lo^T Y -> two partial slots; warp w takes the blocks
+    // b = w / 4 (mod 4) (a warp reaches the 32 TMEM lanes of its index modulo 4)
     const int lane128 = (warp & 3) * 32 + (t & 31);
     const int l = lane128 & 63, half = lane128 >> 6;
     float* out = P.Cp + ((size_t)blockIdx.x * 2 + half) * (size_t)P.kb * P.nb;
     const bool zero = ntl == 0 || (!COR && half == 1);
-    for (int b = warp >> 2; b < nblk; b += 2) {
+    for (int b = warp >> 2; b < nblk; b += kConvWarps / 4) {
       const int irow = 64 * b + l;
 #pragma unroll
       for (int c0 = 0; c0 < 64; c0 += 16) {
