@@ -19,10 +19,9 @@ namespace tsqr_b200 {
 // tc_nn_tma.cu: the TMA-fed form of the update; false = not applicable, nothing launched
 bool launch_tc_nn_tma(bool corrected, IoType io, const void* X, long long ldx, int kb, const float* C, void* Y, long long ldy, int nb,
                       long long M, cudaStream_t s);
-// tc_tn_tma.cu: the TMA-fed form of the coefficient product; returns the number of row ranges (2 partial slots each), 0 = not
-// applicable, nothing launched
-int launch_tc_tn_tma(bool corrected, IoType io, const void* X, long long ldx, int kb, const void* Y, long long ldy, int nb,
-                     long long M, int max_slabs, float* Cp, cudaStream_t s);
+// tc_tn_tma.cu: the TMA-fed form of the coefficient product (C complete on return); false = not applicable, nothing launched
+bool launch_tc_tn_tma(bool corrected, IoType io, const void* X, long long ldx, int kb, const void* Y, long long ldy, int nb,
+                      long long M, int max_slabs, float* Cp, float* C, cudaStream_t s);
 namespace {
 using namespace tc;
 
@@ -236,10 +235,7 @@ void launch_typed(const T* X, long long ldx, int kb, T* Y, long long ldy, int nb
   TSQR_CUDA_CHECK(cudaFuncSetAttribute(tn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTnSmem));
   TSQR_CUDA_CHECK(cudaFuncSetAttribute(nn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kNnSmem));
   const IoType io = sizeof(T) == 2 ? IoType::f16 : IoType::f32;
-  const int ranges = launch_tc_tn_tma(COR, io, X, ldx, kb, Y, ldy, nb, M, nslabs, Cp, s);
-  if (ranges > 0) {
-    reduce(Cp, 2 * ranges, (size_t)kb * nb, C, s);
-  } else {
+  if (!launch_tc_tn_tma(COR, io, X, ldx, kb, Y, ldy, nb, M, nslabs, Cp, C, s)) {
     tn<<<nslabs, kT, kTnSmem, s>>>(X, ldx, kb, Y, ldy, nb, M, rows_per_slab, Cp);
     note_launch();
     reduce(Cp, 2 * nslabs, (size_t)kb * nb, C, s);

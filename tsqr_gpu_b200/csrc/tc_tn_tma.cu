@@ -7,8 +7,9 @@
 //   * the converter threads rewrite a landed block as the K-major tf32 operand (K = rows; 128-byte swizzle; hi in lines [0, 64),
 //     lo = x - hi in lines [64, 128) for the corrected modes) -- conflict-free thread-per-row stores; 16 warps so that the
 //     fence / barrier latencies of one warp hide behind the others;
-//   * D_b[128 x 64] += [X_b hi | X_b lo]^T Y hi (+ ... Y lo) with tcgen05.mma kind::tf32, one accumulator block of 64 TMEM
-//     columns per 64 columns of X, kept in tensor memory over the whole row range;
+//   * corrected modes: D_b[128 x 128] += [X_b hi | X_b lo]^T [Y hi | Y lo] as ONE M = 128, N = 128 product per K step (operand
+//     bytes read from shared memory per product are what bounds this kernel), otherwise D_b[128 x 64] += X_b^T Y; one
+//     accumulator block per 64 columns of X, kept in tensor memory over the whole row range (256 / 512 columns per launch);
 //   * the two accumulator halves (hi^T Y, lo^T Y) leave as two partial slots per CTA, summed in fixed order by the caller.
 // tc_project.cu keeps the thread-staged kernel for matrices TMA cannot address.
 #include <cuda.h>
@@ -50,6 +51,7 @@ template <bool COR, typename TIo>
 __global__ void __launch_bounds__(kThreads + 64, 1) tc_tn_tma_kernel(const TnParams P, const __grid_constant__ CUtensorMap tmapX,
                                                                      const __grid_constant__ CUtensorMap tmapY) {
   using Sm = TnSmem<TIo>;
+  constexpr int kDW = COR ? 128 : 64;   // accumulator columns per 64-column block of X
   extern __shared__ __align__(1024) char sm[];
   const int t = threadIdx.x, warp = t >> 5;
   uint64_t* bar_full = reinterpret_cast<uint64_t*>(sm + Sm::oBar);   // landing slot filled (TMA transaction bytes)
@@ -90,7 +92,7 @@ __global__ void __launch_bounds__(kThreads + 64, 1) tc_tn_tma_kernel(const TnPar
   } else if (warp == kConvWarps) {
     // ---- tensor-core issuer: one thread; product q reads X stage q & 1 and the Y buffer of its tile
     if (t == kConvWarps * 32) {
-      const uint32_t idesc = idesc_tf32(128, 64, false, false, false);
+      const uint32_t idesc = idesc_tf32(128, kDW, false, false, false);
       for (int i = 0; i < ntl; ++i) {
         mbar_wait(bar_ry + (i & 1), (uint32_t)(i >> 1) & 1u);
         const uint32_t ya = smem_u32(sm + Sm::oY + (i & 1) * kOp);
@@ -99,17 +101,14 @@ __global__ void __launch_bounds__(kThreads + 64, 1) tc_tn_tma_kernel(const TnPar
           mbar_wait(bar_rx + (q & 1), (uint32_t)(q >> 1) & 1u);
           fence_after_sync();
           const uint32_t xa = smem_u32(sm + Sm::oX + (q & 1) * kOp);
-          const uint32_t d = tm + 64u * (uint32_t)b;
+          const uint32_t d = tm + (uint32_t)kDW * (uint32_t)b;
 #pragma unroll
           for (int kblk = 0; kblk < 2; ++kblk) {
             const uint64_t da = smem_desc(xa + (uint32_t)kblk * sw::kBlock, 16, 1024, 2);
-            const uint64_t dh = smem_desc(ya + (uint32_t)kblk * sw::kBlock, 16, 1024, 2);
-            const uint64_t dl = smem_desc(ya + (uint32_t)kblk * sw::kBlock + 64u * 128u, 16, 1024, 2);
+            const uint64_t dy = smem_desc(ya + (uint32_t)kblk * sw::kBlock, 16, 1024, 2);   // N = 128: lines [Y hi | Y lo]
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk) {
-              mma_tf32(d, da + (uint64_t)(kk * 2), dh + (uint64_t)(kk * 2), idesc, i > 0 || kblk > 0 || kk > 0);
-              if (COR) mma_tf32(d, da + (uint64_t)(kk * 2), dl + (uint64_t)(kk * 2), idesc, true);
-            }
+            for (int kk = 0; kk < 4; ++kk)
+              mma_tf32(d, da + (uint64_t)(kk * 2), dy + (uint64_t)(kk * 2), idesc, i > 0 || kblk > 0 || kk > 0);
           }
           mma_commit(bar_mma + (q & 1));
         }
@@ -128,33 +127,36 @@ __global__ void __launch_bounds__(kThreads + 64, 1) tc_tn_tma_kernel(const TnPar
     uint32_t offs[8];                       // swizzled chunk of the row inside a 128-byte line, by line % 8
 #pragma unroll
     for (int e = 0; e < 8; ++e) offs[e] = sw::off(row, e);
-    for (int j = 0; j < nitems; ++j) {
-      const int slot = j % kLand, i = j / per, r = j % per;
-      const int q = i * nblk + (r - 1);   // product index of an X item
-      char* op;
-      if (r == 0) {
-        if (i >= 2) wait_product((i - 1) * nblk - 1);   // every product of tile i - 2 read this Y buffer
-        op = sm + Sm::oY + (i & 1) * kOp;
-      } else {
-        if (q >= 2) wait_product(q - 2);                // the product that read this X stage
-        op = sm + Sm::oX + (q & 1) * kOp;
-      }
-      mbar_wait(bar_full + slot, (uint32_t)(j / kLand) & 1u);
-      {
-        static_assert(kColsPerThread == 8, "one 8-line swizzle atom per thread");
-        const TIo* land = reinterpret_cast<const TIo*>(sm + Sm::oLand + slot * Sm::kSlot) + (kColsPerThread * cg) * kTile + row;
-        char* dst = op + (kColsPerThread * cg) * 128;
+    static_assert(kColsPerThread == 8, "one 8-line swizzle atom per thread");
+    const uint32_t land_off = (uint32_t)((kColsPerThread * cg) * kTile + row) * (uint32_t)sizeof(TIo);
+    const uint32_t dst_off = (uint32_t)(kColsPerThread * cg) * 128u;
+    int slot = 0;            // landing ring position and the parity of its current use
+    uint32_t par = 0;
+    // one landed block -> operand buffer `op`; then the slot goes back to the producer and `ready` gets this thread's arrival
+    auto convert = [&](char* op, uint64_t* ready) {
+      mbar_wait(bar_full + slot, par);
+      const TIo* land = reinterpret_cast<const TIo*>(sm + Sm::oLand + slot * Sm::kSlot + land_off);
+      char* dst = op + dst_off;
 #pragma unroll
-        for (int c = 0; c < kColsPerThread; ++c) {
-          const float x = io_plain(land + c * kTile);
-          const float h = to_tf32_rna(x);
-          *reinterpret_cast<float*>(dst + (c & ~7) * 128 + offs[c & 7]) = h;
-          if (COR) *reinterpret_cast<float*>(dst + 64 * 128 + (c & ~7) * 128 + offs[c & 7]) = __fsub_rn(x, h);
-        }
+      for (int c = 0; c < kColsPerThread; ++c) {
+        const float x = io_plain(land + c * kTile);
+        const float h = to_tf32_rna(x);
+        *reinterpret_cast<float*>(dst + offs[c]) = h;
+        if (COR) *reinterpret_cast<float*>(dst + 64 * 128 + offs[c]) = __fsub_rn(x, h);
       }
       fence_async_smem();   // landing-slot reads before the next bulk write; operand stores before the tensor core reads them
       mbar_arrive(bar_empty + slot);
-      mbar_arrive(r == 0 ? bar_ry + (i & 1) : bar_rx + (q & 1));
+      mbar_arrive(ready);
+      if (++slot == kLand) { slot = 0; par ^= 1u; }
+    };
+    int q = 0;   // product index of the next X block
+    for (int i = 0; i < ntl; ++i) {
+      if (i >= 2) wait_product(q - nblk - 1);   // every product of tile i - 2 read this Y buffer
+      convert(sm + Sm::oY + (i & 1) * kOp, bar_ry + (i & 1));
+      for (int b = 0; b < nblk; ++b, ++q) {
+        if (q >= 2) wait_product(q - 2);        // the product that read this X stage
+        convert(sm + Sm::oX + (q & 1) * kOp, bar_rx + (q & 1));
+      }
     }
     if (ntl > 0) wait_product(ntl * nblk - 1);
     fence_after_sync();
@@ -168,8 +170,15 @@ __global__ void __launch_bounds__(kThreads + 64, 1) tc_tn_tma_kernel(const TnPar
       const int irow = 64 * b + l;
 #pragma unroll
       for (int c0 = 0; c0 < 64; c0 += 16) {
-        float v[16];
-        tmem_ld16(tmem_addr(tm + 64 * b, warp, c0), v);
+        float v[16], w[16];
+        tmem_ld16(tmem_addr(tm + kDW * b, warp, c0), v);
+        if (COR) {   // accumulator columns [64, 128) of the hi lanes hold X hi^T Y lo
+          tmem_ld16(tmem_addr(tm + kDW * b, warp, 64 + c0), w);
+          if (half == 0) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) v[e] = __fadd_rn(v[e], w[e]);
+          }
+        }
         if (irow < P.kb) {
 #pragma unroll
           for (int e = 0; e < 16; ++e)
@@ -212,38 +221,59 @@ bool block_map(CUtensorMap* map, const void* A, long long lda, long long M, int 
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// C[k0 + i, c] (ld ldc) = sum over the partial slots, in slot order (bit-reproducible)
+__global__ void tn_sum_slots_kernel(const float* __restrict__ Cp, int slots, int kg, int nb, float* __restrict__ C, long long ldc) {
+  const size_t count = (size_t)kg * nb;
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < count; e += (size_t)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+#pragma unroll 8
+    for (int sl = 0; sl < slots; ++sl) acc += Cp[(size_t)sl * count + e];
+    C[(e % kg) + (e / kg) * ldc] = acc;
+  }
+}
+
 template <bool COR, typename TIo>
-int launch_t(IoType io, const void* X, long long ldx, int kb, const void* Y, long long ldy, int nb, long long M, int max_slabs,
-             float* Cp, cudaStream_t s) {
-  CUtensorMap mx, my;
-  if (!block_map(&mx, X, ldx, M, kb, io) || !block_map(&my, Y, ldy, M, nb, io)) return 0;
+bool launch_t(IoType io, const void* X, long long ldx, int kb, const void* Y, long long ldy, int nb, long long M, int max_slabs,
+              float* Cp, float* C, cudaStream_t s) {
+  constexpr int kmax = COR ? 256 : 512;   // 512 TMEM columns / accumulator columns per block
+  const int ngroups = (kb + kmax - 1) / kmax;
+  const size_t es = io == IoType::f16 ? 2 : 4;
+  CUtensorMap mx[4], my;
+  if (ngroups > 4 || !block_map(&my, Y, ldy, M, nb, io)) return false;
+  for (int gi = 0; gi < ngroups; ++gi)   // every map before the first launch: all or nothing
+    if (!block_map(&mx[gi], static_cast<const char*>(X) + (size_t)gi * kmax * (size_t)ldx * es, ldx, M, std::min(kmax, kb - gi * kmax), io))
+      return false;
   auto kern = tc_tn_tma_kernel<COR, TIo>;
   TSQR_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TnSmem<TIo>::kBytes));
-  TnParams p{};
-  p.kb = kb; p.nb = nb; p.nblk = (kb + 63) / 64; p.M = M; p.Cp = Cp;
-  p.tiles = (int)((M + kTile - 1) / kTile);
-  int grid = std::min(std::min(device_sm_count(), p.tiles), max_slabs);
-  p.tiles_per_cta = (p.tiles + grid - 1) / grid;
-  grid = (p.tiles + p.tiles_per_cta - 1) / p.tiles_per_cta;   // no CTA without a tile
-  kern<<<grid, kThreads + 64, TnSmem<TIo>::kBytes, s>>>(p, mx, my);
-  note_launch();
+  for (int gi = 0; gi < ngroups; ++gi) {
+    const int k0 = gi * kmax, kg = std::min(kmax, kb - k0);
+    TnParams p{};
+    p.kb = kg; p.nb = nb; p.nblk = (kg + 63) / 64; p.M = M; p.Cp = Cp;
+    p.tiles = (int)((M + kTile - 1) / kTile);
+    int grid = std::min(std::min(device_sm_count(), p.tiles), max_slabs);
+    p.tiles_per_cta = (p.tiles + grid - 1) / grid;
+    grid = (p.tiles + p.tiles_per_cta - 1) / p.tiles_per_cta;   // no CTA without a tile
+    kern<<<grid, kThreads + 64, TnSmem<TIo>::kBytes, s>>>(p, mx[gi], my);
+    tn_sum_slots_kernel<<<(kg * nb + 255) / 256, 256, 0, s>>>(Cp, 2 * grid, kg, nb, C + k0, kb);
+    note_launch(2);
+  }
   TSQR_CUDA_CHECK(cudaGetLastError());
-  return grid;
+  return true;
 }
 
 }  // namespace
 
-// Returns the number of row ranges (the caller sums 2 x that many partial slots of kb x nb floats in Cp), or 0 when
-// nothing was launched (TMA cannot address X or Y, kb > 512, or TSQR_B200_TMA=0): the caller runs its thread-staged kernel.
-int launch_tc_tn_tma(bool corrected, IoType io, const void* X, long long ldx, int kb, const void* Y, long long ldy, int nb,
-                     long long M, int max_slabs, float* Cp, cudaStream_t s) {
+// C (kb x nb, ld kb) = X^T Y; Cp: room for 2 x max_slabs partial slots of kb x nb floats. false: nothing was launched (TMA
+// cannot address X or Y, or TSQR_B200_TMA=0) and the caller runs its thread-staged kernel.
+bool launch_tc_tn_tma(bool corrected, IoType io, const void* X, long long ldx, int kb, const void* Y, long long ldy, int nb,
+                      long long M, int max_slabs, float* Cp, float* C, cudaStream_t s) {
   static const bool on = [] { const char* e = std::getenv("TSQR_B200_TMA"); return !(e && e[0] == '0'); }();
-  if (!on || kb < 1 || kb > 512 || max_slabs < 1) return 0;
+  if (!on || kb < 1 || max_slabs < 1) return false;
   if (io == IoType::f32)
-    return corrected ? launch_t<true, float>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, s)
-                     : launch_t<false, float>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, s);
-  return corrected ? launch_t<true, __half>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, s)
-                   : launch_t<false, __half>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, s);
+    return corrected ? launch_t<true, float>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, C, s)
+                     : launch_t<false, float>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, C, s);
+  return corrected ? launch_t<true, __half>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, C, s)
+                   : launch_t<false, __half>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, C, s);
 }
 
 }  // namespace tsqr_b200
