@@ -89,20 +89,30 @@ __global__ void __launch_bounds__(128 * kWg, 1) tc_nn_tma_kernel(const NnParams 
   const int ntl = ntl_cta > wg ? (ntl_cta - wg + kWg - 1) / kWg : 0;
   auto tile_of = [&](int i) { return tile_beg + wg + kWg * i; };
   const int npanels = ntl * npan;
-  auto issue_load = [&](int g) {   // panel g of this pipeline's stream -> slot g % S
-    const int slot = g % S;
-    mbar_arrive_expect_tx(bar_full + slot, Sm::kSlot);
-    tma_load_2d(ring + slot * Sm::kSlot, &tmapX, bar_full + slot, tile_of(g / npan) * 128, 16 * (g % npan));
+  // producer state (thread 0 of the pipeline): the next panel to load, as (tile index, panel, slot)
+  int ld_it = 0, ld_p = 0, ld_slot = 0, ld_left = npanels;
+  auto issue_next = [&]() {
+    mbar_arrive_expect_tx(bar_full + ld_slot, Sm::kSlot);
+    tma_load_2d(ring + ld_slot * Sm::kSlot, &tmapX, bar_full + ld_slot, tile_of(ld_it) * 128, 16 * ld_p);
+    if (++ld_p == npan) { ld_p = 0; ++ld_it; }
+    if (++ld_slot == S) ld_slot = 0;
+    --ld_left;
   };
   if (t == 0)
-    for (int g = 0; g < S && g < npanels; ++g) issue_load(g);
+    for (int i = 0; i < S && ld_left > 0; ++i) issue_next();
   const uint64_t dCh = smem_desc(smem_u32(CHi), 128, kb::sbo(P.kp)), dCl = smem_desc(smem_u32(CLo), 128, kb::sbo(P.kp));
   const uint32_t id = idesc_tf32(128, 64, false, false, false);
-  uint32_t ph_mma[2] = {0, 0};
-  uint32_t commits[2] = {0, 0}, waits[2] = {0, 0};   // per A buffer: commits issued / waited for (uniform over the pipeline)
   TIo* Y = reinterpret_cast<TIo*>(P.Y);
+  int nw = 0;   // products [0, nw) of this pipeline are known complete (commit g arrives on bar_mma[g & 1], parity (g >> 1) & 1)
+  auto wait_product = [&](int q) {
+    while (nw <= q) {
+      mbar_wait(bar_mma + (nw & 1), (uint32_t)(nw >> 1) & 1u);
+      ++nw;
+    }
+  };
+  int g = 0, slot = 0;   // panel counter of the pipeline, its landing slot and the parity of the slot's current use
+  uint32_t par = 0;
 
-  int g = 0;
   for (int it = 0; it < ntl; ++it) {
     const int tile = tile_of(it);
     const long long row = (long long)tile * 128 + t;
@@ -113,10 +123,11 @@ __global__ void __launch_bounds__(128 * kWg, 1) tc_nn_tma_kernel(const NnParams 
 #pragma unroll
       for (int c = 0; c < 64; ++c) yv[c] = (valid && c < P.nb) ? io_plain(yp + (long long)c * P.ldy) : 0.f;
     }
-    for (int p = 0; p < npan; ++p, ++g) {
-      const int slot = g % S, ab = g & 1;
+    uint64_t dp = 0;   // descriptor offset of C rows [16 p, 16 p + 16)
+    for (int p = 0; p < npan; ++p, ++g, dp += 32) {
+      const int ab = g & 1;
       float xh[16], xl[16];
-      mbar_wait(bar_full + slot, (uint32_t)(g / S) & 1u);
+      mbar_wait(bar_full + slot, par);
       {
         const TIo* land = reinterpret_cast<const TIo*>(ring + slot * Sm::kSlot);
 #pragma unroll
@@ -128,14 +139,12 @@ __global__ void __launch_bounds__(128 * kWg, 1) tc_nn_tma_kernel(const NnParams 
       }
       fence_async_smem();   // generic-proxy reads before the async-proxy write that reuses the slot
       mbar_arrive(bar_empty + slot);
-      if (t == 0 && g + S < npanels) {
-        mbar_wait(bar_empty + slot, (uint32_t)(g / S) & 1u);
-        issue_load(g + S);
+      if (t == 0 && ld_left > 0) {
+        mbar_wait(bar_empty + slot, par);
+        issue_next();
       }
-      if (commits[ab] > waits[ab]) {   // the products that read this A buffer two panels ago
-        mbar_wait(bar_mma + ab, ph_mma[ab]);
-        ph_mma[ab] ^= 1;
-        waits[ab]++;
+      if (g >= 2) {   // the products that read this A buffer two panels ago
+        wait_product(g - 2);
         fence_after_sync();
       }
       tmem_st16(tmem_addr(tmAh + 16 * ab, warp, 0), xh);
@@ -147,7 +156,7 @@ __global__ void __launch_bounds__(128 * kWg, 1) tc_nn_tma_kernel(const NnParams 
         fence_after_sync();
 #pragma unroll
         for (int kk = 0; kk < 2; ++kk) {
-          const uint64_t off = (uint64_t)(((uint32_t)p * 512u + (uint32_t)kk * 256u) >> 4);
+          const uint64_t off = dp + (uint64_t)(kk * 16);
           mma_tf32_ts(tmD, tmAh + 16 * ab + 8 * kk, dCh + off, id, p > 0 || kk > 0);
           if (COR) {
             mma_tf32_ts(tmD, tmAh + 16 * ab + 8 * kk, dCl + off, id, true);
@@ -156,16 +165,10 @@ __global__ void __launch_bounds__(128 * kWg, 1) tc_nn_tma_kernel(const NnParams 
         }
         mma_commit(bar_mma + ab);
       }
-      commits[ab]++;
+      if (++slot == S) { slot = 0; par ^= 1u; }
     }
-    // ---- all products of the tile: drain both buffers' commits, then Y_row -= D_row
-#pragma unroll
-    for (int ab = 0; ab < 2; ++ab)
-      while (commits[ab] > waits[ab]) {
-        mbar_wait(bar_mma + ab, ph_mma[ab]);
-        ph_mma[ab] ^= 1;
-        waits[ab]++;
-      }
+    // ---- all products of the tile, then Y_row -= D_row
+    wait_product(g - 1);
     fence_after_sync();
     {
       TIo* yp = Y + row;
