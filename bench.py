@@ -363,6 +363,19 @@ def main():
         f1.record()
         barrier()
         ems = f0.elapsed_time(f1)
+        # the floor of this number: the same bytes moved with no factorisation in between (every rank at once; all of A must
+        # be on the device before any of Q can leave, so the two directions cannot overlap within one factorisation)
+        barrier()
+        f0.record()
+        a.t().copy_(a_host, non_blocking=True)
+        q_host.copy_(q.t(), non_blocking=True)
+        f1.record()
+        barrier()
+        copy_ms = f0.elapsed_time(f1)
+        if P > 1:
+            tt = torch.tensor([copy_ms], device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            copy_ms = float(tt.item())
         if P > 1:
             tt = torch.tensor([ems], device="cuda")
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -370,7 +383,7 @@ def main():
         ems /= e2e_steps
         e2e = {"value": flops(m * P, n) / (ems * 1e-3) / 1e9, "unit": "GFLOP/s", "ms_per_step": ems,
                "steps": e2e_steps, "h2d_bytes_per_step": m * n * esz * P,
-               "d2h_bytes_per_step": (m * n * esz + n * n * 4) * P,
+               "d2h_bytes_per_step": (m * n * esz + n * n * 4) * P, "copies_only_ms": copy_ms,
                "api": (("tsqr_b200_host_pipeline_run (C ABI, csrc/host_pipeline.cu)" if P == 1 else "tsqr_gpu_b200.HostPipeline.run")
                        + ": 8 row slabs per GPU, H2D | reduce and build | D2H overlapped on copy streams"
                        if pipe is not None else "H2D, tsqr_gpu_b200.qr / dist.ShardedTSQR.tsqr, D2H on one stream")}
