@@ -1,14 +1,14 @@
 // BlockQR projection update Y <- Y - X C on sm_100a as a TMA-fed streaming kernel (the second of the two GEMMs per panel
 // of reference src/blockqr.cu:92-116 / :272-291): X is m x kb (columns already factored), C is kb x nb (nb <= 64),
 // Y the current panel. HBM-bound: X is read once, Y read and written once per launch.
-//   * three independent tile pipelines per CTA (one CTA per SM), a tile = 128 rows, thread t = tile row t = TMEM lane t;
+//   * four independent tile pipelines per CTA (one CTA per SM), a tile = 128 rows, thread t = tile row t = TMEM lane t;
 //   * X arrives as 128 x 16 panel boxes (cp.async.bulk.tensor) through a 3-slot ring per pipeline, so global-memory
 //     latency is decoupled from the staging;
 //   * the row's thread moves its 16 values into TENSOR MEMORY as the A operand (tf32 hi, and lo for the corrected
 //     modes; double-buffered), so no transposing shared-memory staging is needed;
 //   * C (hi / lo) stays in shared memory for the whole kernel as the K-major B operand; D += X_p C[16p:16p+16, :] with
 //     tcgen05.mma kind::tf32 (1 or 3 products), fp32 accumulator in TMEM;
-//   * the Y row is loaded at the start of the tile and combined with the accumulator row at the end.
+//   * the Y row is loaded behind the tile's last products and combined with the accumulator row.
 // kb is cut into groups that fit the shared-memory image of C (256 columns corrected, 512 otherwise).
 // tc_project.cu keeps the thread-staged kernel for matrices TMA cannot address (ld * element size not a multiple of 16).
 #include <cuda.h>
@@ -22,9 +22,9 @@ namespace tsqr_b200 {
 namespace {
 using namespace tc;
 
-constexpr int kWg = 3;          // tile pipelines per CTA
+constexpr int kWg = 4;          // tile pipelines per CTA
 constexpr int kSlots = 3;       // landing slots per pipeline
-constexpr int kTmemPerWg = 160; // D [0, 64), A hi [64, 80) / [80, 96), A lo [96, 112) / [112, 128)
+constexpr int kTmemPerWg = 128; // D [0, 64), A hi [64, 80) / [80, 96), A lo [96, 112) / [112, 128)
 
 struct NnParams {
   const float* C;   // kb_all x nb, ld ldc; this launch uses rows [0, kb)
@@ -40,7 +40,7 @@ struct NnParams {
 template <typename TIo>
 struct NnSmem {
   static constexpr uint32_t kSlot = 128u * 16u * sizeof(TIo);
-  static constexpr uint32_t kBarBytes = 256;
+  static constexpr uint32_t kBarBytes = 512;   // kWg x (2 kSlots + 2) mbarriers, then the TMEM slot in the last 8 bytes
   static constexpr uint32_t oBar = 0;
   static constexpr uint32_t oRing = 1024;
   static constexpr uint32_t oC = oRing + kWg * kSlots * kSlot;
@@ -117,12 +117,6 @@ __global__ void __launch_bounds__(128 * kWg, 1) tc_nn_tma_kernel(const NnParams 
     const int tile = tile_of(it);
     const long long row = (long long)tile * 128 + t;
     const bool valid = row < P.M;
-    float yv[64];   // the Y row: in flight while the panels stream
-    {
-      const TIo* yp = Y + row;
-#pragma unroll
-      for (int c = 0; c < 64; ++c) yv[c] = (valid && c < P.nb) ? io_plain(yp + (long long)c * P.ldy) : 0.f;
-    }
     uint64_t dp = 0;   // descriptor offset of C rows [16 p, 16 p + 16)
     for (int p = 0; p < npan; ++p, ++g, dp += 32) {
       const int ab = g & 1;
@@ -167,7 +161,13 @@ __global__ void __launch_bounds__(128 * kWg, 1) tc_nn_tma_kernel(const NnParams 
       }
       if (++slot == S) { slot = 0; par ^= 1u; }
     }
-    // ---- all products of the tile, then Y_row -= D_row
+    // ---- the Y row (its loads fly while the last products finish), all products of the tile, then Y_row -= D_row
+    float yv[64];
+    {
+      const TIo* yp = Y + row;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) yv[c] = (valid && c < P.nb) ? io_plain(yp + (long long)c * P.ldy) : 0.f;
+    }
     wait_product(g - 1);
     fence_after_sync();
     {
