@@ -162,8 +162,8 @@ int tsqr_b200_pc_status(int mode, size_t m, size_t n, const void* ws, void* stre
     TSQR_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
     if (est) std::memcpy(est, &st[2], sizeof(float));
     if (std::getenv("TSQR_B200_PC_PHASES"))   // SM-clock cycles of the single-CTA phases (tuning aid)
-      std::fprintf(stderr, "tsqr_b200 pc phases: sample gather %d sweep %d | finish chol %d inverse %d rest %d\n", st[8], st[9],
-                   st[4], st[5], st[6]);
+      std::fprintf(stderr, "tsqr_b200 pc phases: sample gather %d sweep %d | finish chol %d inverse %d rest %d (copies %d certificate %d)\n",
+                   st[8], st[9], st[4], st[5], st[6], st[10], st[11]);
     return st[0] == kPcOk ? 1 : 0;
   });
 }

@@ -723,7 +723,8 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
 // (warp w adds partials w, w + 8, ...: coalesced 256-byte reads, then the 8 warp sums are added in fixed order).
 // Stage 2, the CTA that finishes last (ticket): chol(G), certificate, R = R_z R_pre, C = R_z^-1, all in fp64 on
 // 64 x 64 matrices in shared memory.
-constexpr int kFinThreads = 256;
+constexpr int kFinThreads = 512;
+constexpr int kFinWarps = kFinThreads / 32;
 __device__ __forceinline__ double rcp_f64(double x) {   // 1/x to fp64 accuracy from the fp32 approximation (x > 0, normal)
   double y = (double)rcp_approx((float)x);
   y = fma(y, fma(-x, y, 1.0), y);
@@ -741,7 +742,10 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
   extern __shared__ __align__(16) char smraw[];
   double* G = reinterpret_cast<double*>(smraw);         // [NP][NP] row-major: trailing matrix of the factorisation, then G^-1
   double* Rz = G + NP * NP;                              // R_z (upper)
-  double* X = Rz + NP * NP;                              // R_z^-1 (upper)
+  constexpr int LX = NP + 1;                              // row stride of X: its transposed reads are conflict free
+  double* X = Rz + NP * NP;                              // R_z^-1 (upper), [NP][LX]
+  double* Rp = X + NP * LX;                              // Rp[k][j] = R_pre[k][j], upper triangle, fp64
+  float* Xf = reinterpret_cast<float*>(Rp + NP * NP);    // fp32 copy of X for the certificate (this GPU runs ~4 DFMA / clock / SM)
   __shared__ double red[kFinThreads / 32][32];
   __shared__ double rdiag[NP];
   __shared__ int s_last, s_bad;
@@ -777,6 +781,11 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
   }
   const long long fclk0 = clock64();
   if (t == 0) s_bad = 0;
+  // R_pre has long left the L2: its loads are issued here and hide behind the factorisation (first use: the R product)
+  for (int e = t; e < NP * NP; e += kFinThreads) {
+    const int k = e % NP, j = e / NP;
+    Rp[k * NP + j] = k <= j ? (double)Rpre[e] : 0.0;
+  }
   // G = HH + LH + LH^T, symmetrised; padded columns get a unit diagonal
   double ssq = 0.0;
   for (int e = t; e < NP * NP; e += kFinThreads) {
@@ -800,7 +809,7 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
   };
   const double nG = sqrt(block_sum(ssq));
   // right-looking Cholesky G = R_z^T R_z with ONE barrier per step: row k of R_z goes to its own array, the
-  // trailing update uses the unscaled row k of G and 1 / G_kk. Thread (warp, lane) owns rows warp + 8a and columns
+  // trailing update uses the unscaled row k of G and 1 / G_kk. Thread (warp, lane) owns rows warp + 16a and columns
   // lane + 32b of the trailing matrix: row k is read with consecutive lanes, G[k][i] is a broadcast.
   for (int k = 0; k < NP; ++k) {
     const double piv = G[k * NP + k];
@@ -818,8 +827,8 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
       if (j > k && j < NP) {
         const double gkj = G[k * NP + j] * inv;
 #pragma unroll
-        for (int a2 = 0; a2 < (NP + 7) / 8; ++a2) {
-          const int i = warp + 8 * a2;
+        for (int a2 = 0; a2 < (NP + kFinWarps - 1) / kFinWarps; ++a2) {
+          const int i = warp + kFinWarps * a2;
           if (i > k && i <= j && i < NP) G[i * NP + j] -= G[k * NP + i] * gkj;
         }
       }
@@ -833,60 +842,71 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
     for (int k = NP - 1; k >= 0; --k) {
       double s = 0.0;
       if (k < c && c < NP)
-        for (int j = k + 1 + g4; j <= c; j += 4) s -= Rz[k * NP + j] * X[j * NP + c];
+        for (int j = k + 1 + g4; j <= c; j += 4) s -= Rz[k * NP + j] * X[j * LX + c];
       s += __shfl_xor_sync(kFull, s, 1);
       s += __shfl_xor_sync(kFull, s, 2);
-      if (g4 == 0 && c < NP) X[k * NP + c] = (k > c) ? 0.0 : ((k == c ? 1.0 : 0.0) + s) * rdiag[k];
+      if (g4 == 0 && c < NP) {
+        const double x = (k > c) ? 0.0 : ((k == c ? 1.0 : 0.0) + s) * rdiag[k];
+        X[k * LX + c] = x;
+        Xf[k * LX + c] = (float)x;
+      }
       __syncwarp();
     }
   }
   __syncthreads();
   const long long fclk2 = clock64();
-  // XT = X^T and the fp64 image of R_pre go over the dead trailing matrix and one more array, so that every product
-  // below reads one broadcast operand and one operand with consecutive lanes
-  double* XT = G;                                        // XT[k][j] = X[j][k]
-  double* Rp = X + NP * NP;                              // Rp[k][j] = R_pre[k][j]
-  for (int e = t; e < NP * NP; e += kFinThreads) {
-    const int k = e / NP, j = e % NP;
-    XT[e] = X[j * NP + k];
-    Rp[e] = (double)Rpre[k + j * NP];
-  }
-  __syncthreads();
-  // G^-1 = X X^T for the certificate: entry (i, j), i = warp + 8a, j = lane + 32b
+  const long long fclk3 = clock64();
+  // |G^-1|_F for the certificate, G^-1 = X X^T, in fp32 (the value is compared with a threshold of 6): entries i <= j,
+  // the off-diagonal ones counted twice; i = warp + 16a, j = lane + 32b. X is upper triangular with explicit zeros
   double ssi = 0.0;
+  {
+    float ssf = 0.f;
 #pragma unroll 1
-  for (int a2 = 0; a2 < (NP + 7) / 8; ++a2) {
-    const int i = warp + 8 * a2;
+    for (int a2 = 0; a2 < (NP + kFinWarps - 1) / kFinWarps; ++a2) {
+      const int i = warp + kFinWarps * a2;
 #pragma unroll
-    for (int b2 = 0; b2 < (NP + 31) / 32; ++b2) {
-      const int j = lane + 32 * b2;
-      if (i < n && j < n) {
-        double s0 = 0.0, s1 = 0.0;
-        int k = max(i, j);
-        for (; k + 1 < NP; k += 2) { s0 += X[i * NP + k] * XT[k * NP + j]; s1 += X[i * NP + k + 1] * XT[(k + 1) * NP + j]; }
-        if (k < NP) s0 += X[i * NP + k] * XT[k * NP + j];
-        ssi += (s0 + s1) * (s0 + s1);
+      for (int b2 = 0; b2 < (NP + 31) / 32; ++b2) {
+        const int j = lane + 32 * b2;
+        if (i < n && j < n && i <= j) {
+          float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll 4
+          for (int k = 0; k < NP; k += 4) {
+            s0 = __fmaf_rn(Xf[i * LX + k], Xf[j * LX + k], s0);
+            s1 = __fmaf_rn(Xf[i * LX + k + 1], Xf[j * LX + k + 1], s1);
+            s2 = __fmaf_rn(Xf[i * LX + k + 2], Xf[j * LX + k + 2], s2);
+            s3 = __fmaf_rn(Xf[i * LX + k + 3], Xf[j * LX + k + 3], s3);
+          }
+          const float v = (s0 + s1) + (s2 + s3);
+          ssf = __fmaf_rn(i == j ? 1.f : 2.f, v * v, ssf);
+        }
       }
     }
+    ssi = (double)ssf;
   }
   const double nGi = sqrt(block_sum(ssi));
   const double est = nG * nGi / (double)n;
+  const long long fclk4 = clock64();
   // R = R_z R_pre (n x n, ld n), C = R_z^-1
 #pragma unroll 1
-  for (int a2 = 0; a2 < (NP + 7) / 8; ++a2) {
-    const int i = warp + 8 * a2;
+  for (int a2 = 0; a2 < (NP + kFinWarps - 1) / kFinWarps; ++a2) {
+    const int i = warp + kFinWarps * a2;
 #pragma unroll
     for (int b2 = 0; b2 < (NP + 31) / 32; ++b2) {
       const int j = lane + 32 * b2;
       if (i < NP && j < NP) {
-        double s0 = 0.0, s1 = 0.0;
-        if (i <= j) {
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        if (i <= j) {   // k in [i, j]: R_z row i is zero left of the diagonal, column j of Rp below it
           int k = i;
-          for (; k + 1 <= j; k += 2) { s0 += Rz[i * NP + k] * Rp[k * NP + j]; s1 += Rz[i * NP + k + 1] * Rp[(k + 1) * NP + j]; }
-          if (k <= j) s0 += Rz[i * NP + k] * Rp[k * NP + j];
+          for (; k + 3 <= j; k += 4) {
+            s0 = fma(Rz[i * NP + k], Rp[k * NP + j], s0);
+            s1 = fma(Rz[i * NP + k + 1], Rp[(k + 1) * NP + j], s1);
+            s2 = fma(Rz[i * NP + k + 2], Rp[(k + 2) * NP + j], s2);
+            s3 = fma(Rz[i * NP + k + 3], Rp[(k + 3) * NP + j], s3);
+          }
+          for (; k <= j; ++k) s0 = fma(Rz[i * NP + k], Rp[k * NP + j], s0);
         }
-        if (i < n && j < n) Rout[i + j * n] = (float)(s0 + s1);
-        const float x = (float)XT[i * NP + j];             // X[j][i]: element (j, i) of the column-major outputs
+        if (i < n && j < n) Rout[i + j * n] = (float)((s0 + s1) + (s2 + s3));
+        const float x = (float)X[j * LX + i];              // element (j, i) of the column-major outputs
         Cmat[j + i * NP] = x;
         Rzinv[j + i * NP] = x;
       }
@@ -901,6 +921,8 @@ __global__ void __launch_bounds__(kFinThreads) pc_finish_kernel(const double* __
     status[4] = (int)(fclk1 - fclk0);          // phase clocks (cycles): G build + Cholesky, inverse, the rest
     status[5] = (int)(fclk2 - fclk1);
     status[6] = (int)(clock64() - fclk2);
+    status[10] = (int)(fclk3 - fclk2);         // of which: (nothing since the transposed copies went), certificate product
+    status[11] = (int)(fclk4 - fclk3);
   }
 }
 
@@ -1082,7 +1104,7 @@ void launch_sample_t(const PcCall& c, cudaStream_t s) {
 template <int NP>
 void launch_finish_t(const PcCall& c, cudaStream_t s, int stage = 0) {
   auto kern = pc_finish_kernel<NP>;
-  const int bytes = 4 * NP * NP * (int)sizeof(double);
+  const int bytes = (4 * NP * NP + NP) * (int)sizeof(double) + NP * (NP + 1) * (int)sizeof(float);   // G, R_z, X (row stride NP + 1), Rp, Xf
   static std::once_flag once;
   std::call_once(once, [&] { set_smem(kern, bytes); });
   const int lanes = (c.cor ? 2 : 1) * NP;
