@@ -147,7 +147,7 @@ int tsqr_b200_orthogonality(int mode, const void* q, size_t ldq, size_t m, size_
 int tsqr_b200_residual(int mode, const void* a, size_t lda, const void* q, size_t ldq, const void* r, size_t ldr, size_t m, size_t n,
                        double* result, void* workspace, size_t workspace_bytes, void* stream);
 
-/* Conditioned test matrix on the device: a (m x n float, n <= 64) = U diag(s) V^T with U, V orthogonal factors of this
+/* Conditioned test matrix on the device: a (m x n float, any n <= m) = U diag(s) V^T with U, V orthogonal factors of this
  * library's QR of counter-based normals (a pure function of `seed`) and s_k = cond^(-k/(n-1)). Replaces
  * mtk::utils::latms (reference src/latms.cu:9-121; singular values of src/test_cond.cu:31-50) without cuRAND/cuSOLVER. */
 size_t tsqr_b200_latms_workspace_bytes(size_t m, size_t n);

@@ -45,7 +45,7 @@ def test_device_metrics_at_full_height(cuda):
     assert abs(orth - o2) < 1e-10 and abs(res - r2) < 1e-10
 
 
-@pytest.mark.parametrize("m,n,cond", [(1 << 17, 64, 1e6), (20000, 32, 1e3), (4096, 7, 10.0)])
+@pytest.mark.parametrize("m,n,cond", [(1 << 17, 64, 1e6), (20000, 32, 1e3), (4096, 7, 10.0), (1 << 15, 128, 1e4), (6000, 200, 1e2)])
 def test_latms_spectrum_and_determinism(cuda, m, n, cond):
     import tsqr_gpu_b200 as tq
     a = tq.latms(m, n, cond, seed=11)

@@ -193,13 +193,13 @@ int tsqr_b200_residual(int mode, const void* a, size_t lda, const void* q, size_
 }
 
 size_t tsqr_b200_latms_workspace_bytes(size_t m, size_t n) {
-  if (m == 0 || n == 0 || n > 64 || n > m) return 256;
+  if (m == 0 || n == 0 || n > m) return 256;
   return latms_workspace_bytes((long long)m, (int)n);
 }
 
 int tsqr_b200_latms(float* a, size_t lda, size_t m, size_t n, float cond, unsigned long long seed, void* ws, size_t ws_bytes,
                     void* stream) {
-  if (m == 0 || n == 0 || n > 64 || n > m) return TSQR_B200_INVALID_SIZE;
+  if (m == 0 || n == 0 || n > m) return TSQR_B200_INVALID_SIZE;
   if (!a || !ws) { set_err("null pointer argument"); return TSQR_B200_ERR_ARGUMENT; }
   return guarded([&] {
     latms(a, (long long)lda, (long long)m, (int)n, cond, seed, (float*)ws, ws_bytes, (cudaStream_t)stream);

@@ -8,7 +8,7 @@ plotting scripts (scripts/*/mk_*graph.py) read results of this library unchanged
   accuracy_cond  header + rows of reference src/test_cond.cu:109-112, 129-248 (mean and standard deviation)
 
 Everything is measured on the device: matrices are made there (uniform by torch's generator, conditioned by
-tsqr_b200_latms for n <= 64), the metrics are the fp64 device kernels of csrc/validate.cu, times are CUDA events.
+tsqr_b200_latms), the metrics are the fp64 device kernels of csrc/validate.cu, times are CUDA events.
 
   python -m tsqr_gpu_b200.csv_driver speed --mode fp32_tc_cor --m-log2 20 24 --n 64 -C 8
 """
@@ -64,15 +64,7 @@ def _uniform(m, n, rand_range, mode, gen):
 
 
 def _conditioned(m, n, cond, mode, seed):
-    if n <= 64:
-        a = api.latms(m, n, cond, seed)
-    else:   # harness-only generator for wide matrices: U diag(s) V^T in fp64 (singular values of src/test_cond.cu:31-50)
-        g = torch.Generator(device="cuda").manual_seed(seed)
-        u, _ = torch.linalg.qr(torch.empty((m, n), dtype=torch.float64, device="cuda").normal_(generator=g))
-        v, _ = torch.linalg.qr(torch.empty((n, n), dtype=torch.float64, device="cuda").normal_(generator=g))
-        s = torch.logspace(0, -math.log10(cond), n, dtype=torch.float64, device="cuda")
-        a = api.to_colmajor(((u * s) @ v.t()).float())
-    return api.to_colmajor(a.to(api.io_dtype(mode)))
+    return api.to_colmajor(api.latms(m, n, cond, seed).to(api.io_dtype(mode)))
 
 
 def _mean_var(xs):
