@@ -53,3 +53,31 @@ def test_library_sharded_driver_single_rank(cuda, oracle):
                 assert oracle.orthogonality(q64) < 5e-6 and oracle.residual(q64, r64, a.cpu().numpy().astype(np.float64)) < 5e-6
     finally:
         lib.tsqr_b200_sharded_destroy(h)
+
+
+def test_two_devices_in_one_process(cuda):
+    """One process driving two GPUs one after the other: everything the library keeps per device (kernel attributes for
+    dynamic shared memory, the constant-memory image slots and their events, the SM count, the static scratch address)
+    must follow the current device. Same input, same bits on both devices."""
+    import numpy as np
+    import torch
+    import tsqr_gpu_b200 as tq
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    outs = []
+    try:
+        for dev in (0, 1):
+            torch.cuda.set_device(dev)
+            for (m, n, mode, reorth) in [(1 << 16, 64, "fp32_tc_cor", False), (20000, 32, "fp32_notc", False),
+                                         (1 << 15, 128, "tf32_tc_cor", True)]:
+                g = torch.Generator(device=f"cuda:{dev}").manual_seed(5)
+                a = tq.to_colmajor(torch.empty((n, m), dtype=torch.float32, device=f"cuda:{dev}").uniform_(-1, 1, generator=g).t())
+                q, r = tq.qr(a, mode, reorth)
+                torch.cuda.synchronize(dev)
+                assert bool(torch.isfinite(q).all()) and float(tq.orthogonality(q, mode)) < 5e-6
+                outs.append((q.cpu(), r.cpu()))
+    finally:
+        torch.cuda.set_device(0)
+    k = len(outs) // 2
+    for (q0, r0), (q1, r1) in zip(outs[:k], outs[k:]):
+        assert torch.equal(q0, q1) and torch.equal(r0, r1)

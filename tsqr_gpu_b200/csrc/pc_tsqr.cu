@@ -18,6 +18,7 @@
 // (R tree) and src/tsqr.cu:143-1061 (backward products).
 #include <cuda.h>
 #include <algorithm>
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -989,6 +990,16 @@ template <typename K>
 void set_smem(K kern, int bytes) {
   TSQR_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
 }
+// the attribute belongs to the device's context: once per kernel instantiation AND device (`done` = bit per device)
+template <typename K>
+void set_smem_once(K kern, int bytes, std::atomic<unsigned long long>& done) {
+  int dev = 0;
+  TSQR_CUDA_CHECK(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (done.load(std::memory_order_acquire) & bit) return;
+  set_smem(kern, bytes);
+  done.fetch_or(bit, std::memory_order_release);
+}
 
 // ---- constant-image slots: a slot is (re)written by a stream-ordered copy only after the event of its previous
 // user has completed on the new user's stream
@@ -1030,8 +1041,8 @@ void img_release(int slot, cudaStream_t s) {
 template <int NP, bool COR, typename TIo, int SLOT>
 void launch_pass1_t(const PcParams& p, const CUtensorMap& map, const CUtensorMap&, int grid, cudaStream_t s) {
   auto kern = pc_gram_kernel<NP, COR, TIo, SLOT>;
-  static std::once_flag once;
-  std::call_once(once, [&] { set_smem(kern, (int)GramSmem<NP>::kBytes); });
+  static std::atomic<unsigned long long> smem_set{0};
+  set_smem_once(kern, (int)GramSmem<NP>::kBytes, smem_set);
   kern<<<grid, 128 * kGrWg, GramSmem<NP>::kBytes, s>>>(p, map);
   note_launch();
   TSQR_CUDA_CHECK(cudaGetLastError());
@@ -1039,8 +1050,8 @@ void launch_pass1_t(const PcParams& p, const CUtensorMap& map, const CUtensorMap
 template <int NP, bool COR, typename TIo, int SLOT>
 void launch_apply_t(const PcParams& p, const CUtensorMap& map, const CUtensorMap& mapq, int grid, cudaStream_t s) {
   auto kern = pc_apply_kernel<NP, COR, TIo, SLOT>;
-  static std::once_flag once;
-  std::call_once(once, [&] { set_smem(kern, (int)ApplySmem<NP, TIo>::kBytes); });
+  static std::atomic<unsigned long long> smem_set{0};
+  set_smem_once(kern, (int)ApplySmem<NP, TIo>::kBytes, smem_set);
   kern<<<grid, 128 * kApWg, ApplySmem<NP, TIo>::kBytes, s>>>(p, map, mapq);
   note_launch();
   TSQR_CUDA_CHECK(cudaGetLastError());
@@ -1094,8 +1105,8 @@ void launch_pass(const PcCall& c, PcParams p, bool want_tma, cudaStream_t s) {
 template <int NP, typename TIo>
 void launch_sample_t(const PcCall& c, cudaStream_t s) {
   auto kern = pc_sample_kernel<NP, TIo>;
-  static std::once_flag once;
-  std::call_once(once, [&] { set_smem(kern, (int)SmpCfg<NP>::kBytes); });
+  static std::atomic<unsigned long long> smem_set{0};
+  set_smem_once(kern, (int)SmpCfg<NP>::kBytes, smem_set);
   kern<<<1, 8 * NP, SmpCfg<NP>::kBytes, s>>>(reinterpret_cast<const TIo*>(c.A), c.lda, c.M, c.n, c.ws + c.L.rpre,
                                               c.ws + c.L.cimg, reinterpret_cast<int*>(c.ws + c.L.status));
   note_launch();
@@ -1105,8 +1116,8 @@ template <int NP>
 void launch_finish_t(const PcCall& c, cudaStream_t s, int stage = 0) {
   auto kern = pc_finish_kernel<NP>;
   const int bytes = (4 * NP * NP + NP) * (int)sizeof(double) + NP * (NP + 1) * (int)sizeof(float);   // G, R_z, X (row stride NP + 1), Rp, Xf
-  static std::once_flag once;
-  std::call_once(once, [&] { set_smem(kern, bytes); });
+  static std::atomic<unsigned long long> smem_set{0};
+  set_smem_once(kern, bytes, smem_set);
   const int lanes = (c.cor ? 2 : 1) * NP;
   const int grid = stage == 2 ? 1 : ((lanes + 31) / 32) * NP;
   kern<<<grid, kFinThreads, bytes, s>>>(reinterpret_cast<const double*>(c.ws + c.L.gpart), c.L.parts,
