@@ -265,10 +265,15 @@ bool launch_t(IoType io, const void* X, long long ldx, int kb, const void* Y, lo
 
 // C (kb x nb, ld kb) = X^T Y; Cp: room for 2 x max_slabs partial slots of kb x nb floats. false: nothing was launched (TMA
 // cannot address X or Y, or TSQR_B200_TMA=0) and the caller runs its thread-staged kernel.
+// tc_tn_tmem.cu: the corrected fp32 modes with the A operand in tensor memory
+bool launch_tc_tn_tmem(const void* X, long long ldx, int kb, const void* Y, long long ldy, int nb, long long M, int max_slabs, float* Cp,
+                       float* C, cudaStream_t s);
+
 bool launch_tc_tn_tma(bool corrected, IoType io, const void* X, long long ldx, int kb, const void* Y, long long ldy, int nb,
                       long long M, int max_slabs, float* Cp, float* C, cudaStream_t s) {
   static const bool on = [] { const char* e = std::getenv("TSQR_B200_TMA"); return !(e && e[0] == '0'); }();
   if (!on || kb < 1 || max_slabs < 1) return false;
+  if (corrected && io == IoType::f32 && launch_tc_tn_tmem(X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, C, s)) return true;
   if (io == IoType::f32)
     return corrected ? launch_t<true, float>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, C, s)
                      : launch_t<false, float>(io, X, ldx, kb, Y, ldy, nb, M, max_slabs, Cp, C, s);
