@@ -93,3 +93,22 @@ def test_blockqr_tensor_core_wider_than_the_tmem_accumulators(cuda, oracle, reor
     assert orth < (5e-6 if reorth else 2e-4)
     _, rl = oracle.lapack_qr(a_in, np.float64)
     assert oracle.r_rel_diff(r, rl) < (3e-5 if reorth else 1e-3)
+
+
+@pytest.mark.parametrize("mode,reorth", [("fp32_tc_cor", False), ("tf32_tc_cor", True), ("fp32_tc_nocor", True), ("fp16_tc_nocor", True)])
+def test_blockqr_many_tiles_per_cta(cuda, mode, reorth):
+    """2^17 x 256: 2048 row tiles of 64 over 148 CTAs, i.e. 14 tiles per CTA in the projection kernels (the shapes above give
+    every CTA one tile). The first tensor-memory form of the coefficient product passed those and hung here: its two
+    consumer groups shared one landing ring and a parity wait cannot tell phase k from phase k - 2. Metrics on the device."""
+    import torch
+    import tsqr_gpu_b200 as tq
+    m, n = 1 << 17, 256
+    g = torch.Generator(device="cuda").manual_seed(17)
+    a = tq.to_colmajor(torch.empty((n, m), dtype=torch.float32, device="cuda").uniform_(-1, 1, generator=g).t().to(tq.io_dtype(mode)))
+    a0 = a.clone()
+    q, r = tq.qr(a, mode, reorth)
+    torch.cuda.synchronize()
+    orth, res = float(tq.orthogonality(q, mode)), float(tq.residual(a0, q, r, mode))
+    print(f"{mode} {m}x{n} reorth={reorth}: orthogonality {orth:.2e} residual {res:.2e}")
+    tol = 5e-6 if mode.endswith("_cor") else 5e-3
+    assert orth < tol and res < tol
