@@ -222,13 +222,22 @@ bool block_map(CUtensorMap* map, const void* A, long long lda, long long M, int 
 }
 
 // C[k0 + i, c] (ld ldc) = sum over the partial slots, in slot order (bit-reproducible)
-__global__ void tn_sum_slots_kernel(const float* __restrict__ Cp, int slots, int kg, int nb, float* __restrict__ C, long long ldc) {
+__global__ void __launch_bounds__(256) tn_sum_slots_kernel(const float* __restrict__ Cp, int slots, int kg, int nb, float* __restrict__ C, long long ldc) {
+  // 64 elements per CTA x 4 slot groups: thread (e, sg) adds slots sg, sg + 4, ...; the four sums are added in fixed order
+  __shared__ float part[4][64];
   const size_t count = (size_t)kg * nb;
-  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < count; e += (size_t)gridDim.x * blockDim.x) {
-    float acc = 0.f;
+  const int sg = threadIdx.x >> 6;
+  const size_t e = (size_t)blockIdx.x * 64 + (threadIdx.x & 63);
+  float acc = 0.f;
+  if (e < count) {
 #pragma unroll 8
-    for (int sl = 0; sl < slots; ++sl) acc += Cp[(size_t)sl * count + e];
-    C[(e % kg) + (e / kg) * ldc] = acc;
+    for (int sl = sg; sl < slots; sl += 4) acc += Cp[(size_t)sl * count + e];
+  }
+  part[sg][threadIdx.x & 63] = acc;
+  __syncthreads();
+  if (sg == 0 && e < count) {
+    const int i = threadIdx.x;
+    C[(e % kg) + (e / kg) * ldc] = (part[0][i] + part[1][i]) + (part[2][i] + part[3][i]);
   }
 }
 
@@ -254,7 +263,7 @@ bool launch_t(IoType io, const void* X, long long ldx, int kb, const void* Y, lo
     p.tiles_per_cta = (p.tiles + grid - 1) / grid;
     grid = (p.tiles + p.tiles_per_cta - 1) / p.tiles_per_cta;   // no CTA without a tile
     kern<<<grid, kThreads + 64, TnSmem<TIo>::kBytes, s>>>(p, mx[gi], my);
-    tn_sum_slots_kernel<<<(kg * nb + 255) / 256, 256, 0, s>>>(Cp, 2 * grid, kg, nb, C + k0, kb);
+    tn_sum_slots_kernel<<<(kg * nb + 63) / 64, 256, 0, s>>>(Cp, 2 * grid, kg, nb, C + k0, kb);
     note_launch(2);
   }
   TSQR_CUDA_CHECK(cudaGetLastError());
