@@ -1,5 +1,5 @@
 """GPU tests of the preconditioned-Cholesky TSQR passes (tsqr_gpu_b200/csrc/pc_tsqr.cu), the fast path of the
-*_tc_* modes for m >= 16384:
+*_tc_* modes (tensor-core passes) and of fp32_notc / fp16_notc (the same passes on the CUDA cores) for m >= 16384:
   * probe: the two passes with caller-supplied R_pre / C against fp64 numpy -- isolates the TMA tile load,
     the tensor-memory A operand of the substitution / Q products and the 128-byte-swizzled Gram operand;
   * end to end through the C ABI against host LAPACK on uniform and kappa = 1e6 inputs (fast path taken);
@@ -35,7 +35,8 @@ def _probe_inputs(m, n, seed):
 @pytest.mark.parametrize("mode,m,n,lda_pad", [
     ("fp32_tc_cor", 16384, 64, 0), ("fp32_tc_cor", 20000, 64, 4), ("tf32_tc_cor", 16500, 32, 0),
     ("fp32_tc_cor", 16400, 16, 8), ("fp32_tc_cor", 17000, 40, 0), ("fp32_tc_nocor", 16384, 64, 0),
-    ("fp16_tc_nocor", 16384, 64, 8), ("fp32_tc_cor", 1 << 18, 64, 0)])
+    ("fp16_tc_nocor", 16384, 64, 8), ("fp32_tc_cor", 1 << 18, 64, 0),
+    ("fp32_notc", 20000, 64, 4), ("fp32_notc", 16500, 32, 0), ("fp32_notc", 17000, 10, 4), ("fp16_notc", 16384, 48, 8)])
 def test_probe_passes_match_numpy(cuda, mode, m, n, lda_pad, use_tma):
     import tsqr_gpu_b200 as tq
     a, rpre, c = _probe_inputs(m, n, seed=m + n)
@@ -48,7 +49,7 @@ def test_probe_passes_match_numpy(cuda, mode, m, n, lda_pad, use_tma):
     z = np.linalg.solve(rpre[:n, :n].astype(np.float64).T, a64.T).T            # Z = A R_pre^-1
     qref = z @ c[:n, :n].astype(np.float64)
     cor = mode in ("fp32_tc_cor", "tf32_tc_cor")
-    tol = 2e-6 if cor else 3e-3
+    tol = 2e-6 if (cor or mode == "fp32_notc") else 3e-3
     qerr = np.abs(q.float().cpu().numpy()[:, :n] - qref).max() / np.abs(qref).max()
     g = gsum.cpu().numpy()
     hh, lh = g[:NP, :NP], g[NP:, :NP]
@@ -77,7 +78,7 @@ def _run(oracle, a, mode):
     return st, est, oracle.orthogonality(q64), oracle.residual(q64, r64, a_in), oracle.r_rel_diff(r64, rl)
 
 
-@pytest.mark.parametrize("mode", ["fp32_tc_cor", "tf32_tc_cor"])
+@pytest.mark.parametrize("mode", ["fp32_tc_cor", "tf32_tc_cor", "fp32_notc"])
 @pytest.mark.parametrize("m,n", [(16384, 64), (70001, 64), (1 << 18, 32), (40000, 16), (1 << 17, 48), (30000, 7)])
 def test_fast_path_matches_lapack(cuda, oracle, mode, m, n):
     a = oracle.uniform_matrix(m, n, seed=500 + n)
@@ -87,7 +88,7 @@ def test_fast_path_matches_lapack(cuda, oracle, mode, m, n):
     assert orth < 2e-6 and res < 2e-6 and rd < 2e-5
 
 
-@pytest.mark.parametrize("mode", ["fp32_tc_nocor", "tf32_tc_nocor", "fp16_tc_nocor"])
+@pytest.mark.parametrize("mode", ["fp32_tc_nocor", "tf32_tc_nocor", "fp16_tc_nocor", "fp16_notc"])
 def test_fast_path_uncorrected_modes(cuda, oracle, mode):
     a = oracle.uniform_matrix(1 << 17, 64, seed=77)
     st, est, orth, res, rd = _run(oracle, a, mode)
@@ -105,16 +106,18 @@ def test_fast_path_uncorrected_modes_conditioned(cuda, oracle, mode):
     assert orth < 5e-3 and res < 5e-3
 
 
+@pytest.mark.parametrize("mode", ["fp32_tc_cor", "fp32_notc"])
 @pytest.mark.parametrize("cond", [1e3, 1e6])
-def test_fast_path_conditioned(cuda, oracle, cond):
+def test_fast_path_conditioned(cuda, oracle, cond, mode):
     a = oracle.latms_matrix(1 << 17, 64, cond, seed=31)
-    st, est, orth, res, _ = _run(oracle, a, "fp32_tc_cor")
-    print(f"cond {cond:g}: status {st} est {est:.3f} orth {orth:.2e} res {res:.2e}")
+    st, est, orth, res, _ = _run(oracle, a, mode)
+    print(f"{mode} cond {cond:g}: status {st} est {est:.3f} orth {orth:.2e} res {res:.2e}")
     assert st == 1 and orth < 2e-6 and res < 2e-6
 
 
+@pytest.mark.parametrize("mode", ["fp32_tc_cor", "fp32_notc"])
 @pytest.mark.parametrize("case", ["graded_rows", "zero_head", "zero_column", "rank_deficient"])
-def test_certificate_rejects_and_householder_takes_over(cuda, oracle, case):
+def test_certificate_rejects_and_householder_takes_over(cuda, oracle, case, mode):
     m, n = 1 << 16, 64
     a = oracle.uniform_matrix(m, n, seed=9)
     if case == "graded_rows":
@@ -126,8 +129,8 @@ def test_certificate_rejects_and_householder_takes_over(cuda, oracle, case):
         a[:, 11] = 0.0
     else:
         a[:, 20] = a[:, 3]
-    st, est, orth, res, _ = _run(oracle, a, "fp32_tc_cor")
-    print(f"{case}: status {st} est {est} orth {orth:.2e} res {res:.2e}")
+    st, est, orth, res, _ = _run(oracle, a, mode)
+    print(f"{mode} {case}: status {st} est {est} orth {orth:.2e} res {res:.2e}")
     if case in ("zero_head", "zero_column"):   # the other two may or may not pass the certificate (a duplicated column
         assert st == 0, "the certificate must reject this input"   # leaves a rounding-level pivot: a valid QR either way)
     assert res < 5e-6

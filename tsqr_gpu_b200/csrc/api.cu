@@ -137,13 +137,13 @@ int tsqr_b200_tsqr_build(int mode, void* q, size_t ldq, const void* a, size_t ld
 
 int tsqr_b200_pc_probe(int mode, const void* a, size_t lda, size_t m, size_t n, const float* rpre, const float* c,
                        void* q, size_t ldq, double* gsum, int use_tma, void* ws, size_t ws_bytes, void* stream) {
-  if (!mode_valid(mode) || !mode_is_tc(mode)) { set_err("the probe takes a *_tc_* mode"); return TSQR_B200_ERR_ARGUMENT; }
+  if (!mode_valid(mode) || !(mode_is_tc(mode) || mode_is_notc_fast(mode))) { set_err("the probe takes a *_tc_* or *_notc mode"); return TSQR_B200_ERR_ARGUMENT; }
   if (m == 0 || n == 0 || n > (size_t)kMaxN) return TSQR_B200_INVALID_SIZE;
   return guarded([&] {
     PcCall call{};
     call.A = a; call.lda = (long long)lda; call.M = (long long)m; call.n = (int)n;
     call.Q = q; call.ldq = (long long)ldq;
-    call.io = mode_io(mode); call.cor = mode_is_cor(mode);
+    call.io = mode_io(mode); call.cor = mode_is_cor(mode); call.notc = !mode_is_tc(mode);
     call.ws = (float*)ws; call.L = pc_layout((long long)m, (int)n);
     if (call.L.total * sizeof(float) > ws_bytes) throw std::runtime_error("tsqr_b200: workspace too small");
     pc_probe(call, rpre, c, gsum, use_tma != 0, (cudaStream_t)stream);

@@ -155,6 +155,11 @@ bool pc_enabled() {
   return on;
 }
 
+bool pc_notc_enabled() {
+  static const bool on = [] { const char* e = std::getenv("TSQR_B200_PC_NOTC"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 Plan make_plan_for(int mode, long long m, int n) {
   Plan plan = make_plan(m, n, 0, use_tc(mode, m));
   if (use_pc(mode, m)) {
@@ -167,9 +172,13 @@ Plan make_plan_for(int mode, long long m, int n) {
 }
 
 size_t plan_floats_any(long long m, int n) {
-  size_t tcf = make_plan(m, n, 0, true).total_floats;
-  if (m >= kPcMinRows) tcf = align_up(tcf, 64) + pc_layout(m, n).total;
-  return std::max(make_plan(m, n, 0, false).total_floats, tcf);
+  size_t tcf = make_plan(m, n, 0, true).total_floats, ccf = make_plan(m, n, 0, false).total_floats;
+  if (m >= kPcMinRows) {
+    const size_t pc = pc_layout(m, n).total;
+    tcf = align_up(tcf, 64) + pc;
+    ccf = align_up(ccf, 64) + pc;
+  }
+  return std::max(ccf, tcf);
 }
 
 size_t tsqr_workspace_bytes(long long m, int n) { return plan_floats_any(m, n) * sizeof(float) + 256; }
@@ -220,6 +229,7 @@ static PcCall pc_call(const Plan& plan, int mode, const void* a, long long lda, 
   c.Q = q; c.ldq = ldq;
   c.io = mode_io(mode);
   c.cor = mode_is_cor(mode);
+  c.notc = !mode_is_tc(mode);
   c.ws = ws + plan.pc_off;
   c.L = plan.pcl;
   return c;
@@ -245,13 +255,22 @@ const float* tsqr_reduce(const Plan& plan, int mode, const void* a, long long ld
     }
     return rout ? rout : ws + plan.levels.back().S_off;
   }
+  const int* skip = nullptr;
+  float* rout = nullptr;
+  if (plan.pc) {   // *_notc fast path (CUDA-core passes); the levels below return at once when its certificate passed
+    pc_reduce(pc_call(plan, mode, a, lda, q, ldq, ws), s);
+    skip = reinterpret_cast<const int*>(ws + plan.pc_off + plan.pcl.status);
+    rout = ws + plan.pc_off + plan.pcl.rout;
+  }
   for (size_t li = 0; li < plan.levels.size(); ++li) {
     PassParams p = level_params(plan, li, a, lda, ws);
     p.emu = mode_emu(mode);
+    p.skip_ok = skip;
+    if (rout && li + 1 == plan.levels.size()) { p.S = rout; p.lds = plan.n; }   // one home for R, whoever wrote it
     ProfScope prof(s, (int)li * 2);
     launch_pass_simt(p, false, li == 0 ? mode_io(mode) : IoType::f32, IoType::f32, s);
   }
-  return ws + plan.levels.back().S_off;
+  return rout ? rout : ws + plan.levels.back().S_off;
 }
 
 void tsqr_build(const Plan& plan, int mode, const void* a, long long lda, void* q, long long ldq,
@@ -274,10 +293,17 @@ void tsqr_build(const Plan& plan, int mode, const void* a, long long lda, void* 
     }
     return;
   }
+  const int* skip = nullptr;
+  if (plan.pc) {
+    ProfScope prof(s, 103);
+    pc_build(pc_call(plan, mode, a, lda, q, ldq, ws), B, ldb, s);
+    skip = reinterpret_cast<const int*>(ws + plan.pc_off + plan.pcl.status);
+  }
   for (size_t li = plan.levels.size(); li-- > 0;) {
     const Level& L = plan.levels[li];
     PassParams p = level_params(plan, li, a, lda, ws);
     p.emu = mode_emu(mode);
+    p.skip_ok = skip;
     ProfScope prof(s, (int)li * 2 + 1);
     if (li + 1 == plan.levels.size()) {
       p.Bsrc = B;

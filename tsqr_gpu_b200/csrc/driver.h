@@ -64,7 +64,12 @@ inline bool mode_is_cor(int m) { return m == fp32_tc_cor || m == tf32_tc_cor; }
 constexpr long long kTcMinRows = 1024;
 inline bool use_tc(int mode, long long m) { return mode_is_tc(mode) && m >= kTcMinRows; }
 bool pc_enabled();   // TSQR_B200_PC=0 switches the fast path off (Householder passes only)
-inline bool use_pc(int mode, long long m) { return mode_is_tc(mode) && m >= kPcMinRows && pc_enabled(); }
+bool pc_notc_enabled();   // TSQR_B200_PC_NOTC=0 keeps the *_notc modes on the Householder passes
+// the two plain CUDA-core modes take the fast path with CUDA-core passes (the _emu modes keep their emulated rounding)
+inline bool mode_is_notc_fast(int m) { return m == fp32_notc || m == fp16_notc; }
+inline bool use_pc(int mode, long long m) {
+  return m >= kPcMinRows && pc_enabled() && (mode_is_tc(mode) || (mode_is_notc_fast(mode) && pc_notc_enabled()));
+}
 Plan make_plan_for(int mode, long long m, int n);
 // workspace floats that cover every mode's plan
 size_t plan_floats_any(long long m, int n);

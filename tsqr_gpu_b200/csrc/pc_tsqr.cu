@@ -719,6 +719,160 @@ __global__ void __launch_bounds__(128 * kApWg, 1) pc_apply_kernel(const PcParams
   __syncthreads();
   if (tid < 32) tmem_dealloc<512>(*tmem_slot);
 }
+// ======================================================================================= CUDA-core passes (*_notc modes)
+// The same two passes in plain fp32 on the CUDA cores, one row per thread and no cross-thread traffic in the substitution:
+//   z = a R_pre^-1 panel by panel: y_p = a_p - sum_{q<p} z_q R[q, p] (R from shared memory, broadcast), then the 16 x 16
+//   diagonal solve with the constant-memory image (solve_panel16, the code the tensor-core passes use);
+//   pass 1: the tile's Z goes through shared memory for G += Z^T Z as a register-blocked rank-128 update (thread (ty, tx)
+//           owns a (NP/16) x (NP/8) block of G in fp32 over at most 16 tiles, then adds it to its fp64 partial);
+//   pass 2: q = z C with C broadcast from shared memory.
+// Both passes run solve_row() on the same inputs, so Z is the same to the bit. Grid = the partial slots of the layout
+// (3 per SM), 128 threads, ~50 KB of shared memory: three CTAs per SM.
+template <int NP>
+__device__ __forceinline__ void solve_row(float (&y)[NP], const float* __restrict__ ci, const float* __restrict__ Rs) {
+  constexpr int NPAN = NP / 16;
+#pragma unroll
+  for (int p = 0; p < NPAN; ++p) {
+#pragma unroll
+    for (int q = 0; q < p; ++q) {   // y_p -= z_q R[16q : 16q+16, 16p : 16p+16]; Rs[k][c] row-major, ld NP
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float z = y[16 * q + i];
+#pragma unroll
+        for (int j4 = 0; j4 < 4; ++j4) {
+          const float4 r = *reinterpret_cast<const float4*>(Rs + (16 * q + i) * NP + 16 * p + 4 * j4);
+          y[16 * p + 4 * j4 + 0] = __fmaf_rn(-z, r.x, y[16 * p + 4 * j4 + 0]);
+          y[16 * p + 4 * j4 + 1] = __fmaf_rn(-z, r.y, y[16 * p + 4 * j4 + 1]);
+          y[16 * p + 4 * j4 + 2] = __fmaf_rn(-z, r.z, y[16 * p + 4 * j4 + 2]);
+          y[16 * p + 4 * j4 + 3] = __fmaf_rn(-z, r.w, y[16 * p + 4 * j4 + 3]);
+        }
+      }
+    }
+    float yp[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) yp[j] = y[16 * p + j];
+    solve_panel16(yp, ci, p);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) y[16 * p + j] = yp[j];
+  }
+}
+
+template <int NP>
+struct NotcSmem {
+  static constexpr int kZld = NP + 4;                              // row stride of the Z tile: conflict-free 128-bit row stores
+  static constexpr uint32_t oR = 0;                                // R_pre, row-major [NP][NP]
+  static constexpr uint32_t oZ = oR + NP * NP * 4;                 // pass 1: Z tile [128][kZld]; pass 2: C, row-major [NP][NP]
+  static constexpr uint32_t kBytes1 = oZ + 128 * kZld * 4;
+  static constexpr uint32_t kBytes2 = oZ + NP * NP * 4;
+};
+
+template <int NP, typename TIo, int SLOT>
+__global__ void __launch_bounds__(128, 3) pc_gram_notc_kernel(const PcParams P) {
+  using Sm = NotcSmem<NP>;
+  constexpr int RW = NP / 16, CW = NP / 8;   // this thread's block of G: rows [RW ty, +RW), columns [CW tx, +CW)
+  extern __shared__ __align__(16) char sm[];
+  float* Rs = reinterpret_cast<float*>(sm + Sm::oR);
+  float* Zs = reinterpret_cast<float*>(sm + Sm::oZ);
+  const float* ci = cimg<SLOT>();
+  const int t = threadIdx.x, ty = t >> 3, tx = t & 7;
+  const TIo* A = reinterpret_cast<const TIo*>(P.A);
+  for (int idx = t; idx < NP * NP; idx += 128) Rs[(idx % NP) * NP + idx / NP] = P.Rpre[idx];   // Rpre[k + c NP] -> Rs[k][c]
+  __syncthreads();
+  float acc[RW][CW];
+#pragma unroll
+  for (int i = 0; i < RW; ++i)
+#pragma unroll
+    for (int j = 0; j < CW; ++j) acc[i][j] = 0.f;
+  double* gp = P.Gpart + (size_t)blockIdx.x * NP * 128;   // slot of this CTA: entry (line i, column j) at j * 128 + i
+  bool first_flush = true;
+  auto flush = [&]() {
+#pragma unroll
+    for (int i = 0; i < RW; ++i)
+#pragma unroll
+      for (int j = 0; j < CW; ++j) {
+        double* g = gp + (size_t)(CW * tx + j) * 128 + (RW * ty + i);
+        *g = (first_flush ? 0.0 : *g) + (double)acc[i][j];
+        acc[i][j] = 0.f;
+      }
+    first_flush = false;
+  };
+  int since = 0;
+  for (int tile = blockIdx.x; tile < P.tiles; tile += gridDim.x) {
+    const long long row = (long long)tile * kPcTileRows + t;
+    const bool valid = row < P.M;
+    float y[NP];
+#pragma unroll
+    for (int c = 0; c < NP; ++c) y[c] = (valid && c < P.n) ? io_plain(A + row + (long long)c * P.lda) : 0.f;
+    solve_row<NP>(y, ci, Rs);
+    __syncthreads();   // the previous tile's update has read Zs
+#pragma unroll
+    for (int c4 = 0; c4 < NP / 4; ++c4)
+      *reinterpret_cast<float4*>(Zs + t * Sm::kZld + 4 * c4) = make_float4(y[4 * c4], y[4 * c4 + 1], y[4 * c4 + 2], y[4 * c4 + 3]);
+    __syncthreads();
+#pragma unroll 4
+    for (int k = 0; k < 128; ++k) {
+      float a[RW], b[CW];
+#pragma unroll
+      for (int i = 0; i < RW; ++i) a[i] = Zs[k * Sm::kZld + RW * ty + i];
+#pragma unroll
+      for (int j = 0; j < CW; ++j) b[j] = Zs[k * Sm::kZld + CW * tx + j];
+#pragma unroll
+      for (int i = 0; i < RW; ++i)
+#pragma unroll
+        for (int j = 0; j < CW; ++j) acc[i][j] = __fmaf_rn(a[i], b[j], acc[i][j]);
+    }
+    if (++since == 16) { flush(); since = 0; }
+  }
+  flush();   // CTAs without tiles write zeros: the finish kernel sums every slot
+}
+
+template <int NP, typename TIo, int SLOT>
+__global__ void __launch_bounds__(128, 3) pc_apply_notc_kernel(const PcParams P) {
+  using Sm = NotcSmem<NP>;
+  extern __shared__ __align__(16) char sm[];
+  if (*P.status != kPcOk) return;   // the Householder passes behind this launch do the work
+  float* Rs = reinterpret_cast<float*>(sm + Sm::oR);
+  float* Cs = reinterpret_cast<float*>(sm + Sm::oZ);
+  const float* ci = cimg<SLOT>();
+  const int t = threadIdx.x;
+  const TIo* A = reinterpret_cast<const TIo*>(P.A);
+  TIo* Q = reinterpret_cast<TIo*>(P.Q);
+  for (int idx = t; idx < NP * NP; idx += 128) {
+    Rs[(idx % NP) * NP + idx / NP] = P.Rpre[idx];
+    Cs[(idx % NP) * NP + idx / NP] = P.C[idx];   // C[k + c NP] -> Cs[k][c]
+  }
+  __syncthreads();
+  for (int tile = blockIdx.x; tile < P.tiles; tile += gridDim.x) {
+    const long long row = (long long)tile * kPcTileRows + t;
+    const bool valid = row < P.M;
+    float y[NP];
+#pragma unroll
+    for (int c = 0; c < NP; ++c) y[c] = (valid && c < P.n) ? io_plain(A + row + (long long)c * P.lda) : 0.f;
+    solve_row<NP>(y, ci, Rs);
+    float q[NP];
+#pragma unroll
+    for (int c = 0; c < NP; ++c) q[c] = 0.f;
+#pragma unroll 4
+    for (int k = 0; k < NP; ++k) {   // C is upper triangular, but a fixed trip count keeps the accumulators in registers
+      const float z = y[k];
+#pragma unroll
+      for (int c4 = 0; c4 < NP / 4; ++c4) {
+        const float4 cc = *reinterpret_cast<const float4*>(Cs + k * NP + 4 * c4);
+        q[4 * c4 + 0] = __fmaf_rn(z, cc.x, q[4 * c4 + 0]);
+        q[4 * c4 + 1] = __fmaf_rn(z, cc.y, q[4 * c4 + 1]);
+        q[4 * c4 + 2] = __fmaf_rn(z, cc.z, q[4 * c4 + 2]);
+        q[4 * c4 + 3] = __fmaf_rn(z, cc.w, q[4 * c4 + 3]);
+      }
+    }
+    if (valid) {
+      TIo* qp = Q + row;
+#pragma unroll
+      for (int c = 0; c < NP; ++c)
+        if (c < P.n) io_store(qp + (long long)c * P.ldq, q[c]);
+    }
+  }
+}
+
 // ======================================================================================= finish
 // Stage 1, every CTA: fp64 sum of the per-CTA partials for 32 consecutive accumulator lanes of one Gram column
 // (warp w adds partials w, w + 8, ...: coalesced 256-byte reads, then the 8 warp sums are added in fixed order).
@@ -1078,9 +1232,53 @@ void launch_np(int slot, const PcParams& p, const CUtensorMap& map, const CUtens
   else if (cor) launch_slot<PASS, NP, true, float>(slot, p, map, mapq, grid, s);
   else launch_slot<PASS, NP, false, float>(slot, p, map, mapq, grid, s);
 }
+// CUDA-core passes of the *_notc modes: one CTA per partial slot of the layout
+template <int PASS, int NP, typename TIo, int SLOT>
+void launch_notc_t(const PcParams& p, int grid, cudaStream_t s) {
+  static std::atomic<unsigned long long> smem_set{0};
+  if (PASS == 1) {
+    auto kern = pc_gram_notc_kernel<NP, TIo, SLOT>;
+    set_smem_once(kern, (int)NotcSmem<NP>::kBytes1, smem_set);
+    kern<<<grid, 128, NotcSmem<NP>::kBytes1, s>>>(p);
+  } else {
+    auto kern = pc_apply_notc_kernel<NP, TIo, SLOT>;
+    set_smem_once(kern, (int)NotcSmem<NP>::kBytes2, smem_set);
+    kern<<<grid, 128, NotcSmem<NP>::kBytes2, s>>>(p);
+  }
+  note_launch();
+  TSQR_CUDA_CHECK(cudaGetLastError());
+}
+template <int PASS, int NP, typename TIo>
+void launch_notc_slot(int slot, const PcParams& p, int grid, cudaStream_t s) {
+  switch (slot) {
+    case 0: launch_notc_t<PASS, NP, TIo, 0>(p, grid, s); break;
+    case 1: launch_notc_t<PASS, NP, TIo, 1>(p, grid, s); break;
+    default: launch_notc_t<PASS, NP, TIo, 2>(p, grid, s); break;
+  }
+}
+template <int PASS>
+void launch_notc(const PcCall& c, const PcParams& p, cudaStream_t s) {
+  const int grid = (int)c.L.parts;
+  const int slot = img_acquire(c.ws + c.L.cimg, s);
+  if (c.io == IoType::f16) {
+    switch (c.L.np) {
+      case 16: launch_notc_slot<PASS, 16, __half>(slot, p, grid, s); break;
+      case 32: launch_notc_slot<PASS, 32, __half>(slot, p, grid, s); break;
+      default: launch_notc_slot<PASS, 64, __half>(slot, p, grid, s); break;
+    }
+  } else {
+    switch (c.L.np) {
+      case 16: launch_notc_slot<PASS, 16, float>(slot, p, grid, s); break;
+      case 32: launch_notc_slot<PASS, 32, float>(slot, p, grid, s); break;
+      default: launch_notc_slot<PASS, 64, float>(slot, p, grid, s); break;
+    }
+  }
+  img_release(slot, s);
+}
 // pass 1 (PASS = 1: pc_gram_kernel, swizzled 32-row boxes) or pass 2 (PASS = 2: pc_apply_kernel, 128 x 16 boxes)
 template <int PASS>
 void launch_pass(const PcCall& c, PcParams p, bool want_tma, cudaStream_t s) {
+  if (c.notc) { launch_notc<PASS>(c, p, s); return; }
   const int np = c.L.np;
   CUtensorMap map, mapq;
   memset(&map, 0, sizeof(map));

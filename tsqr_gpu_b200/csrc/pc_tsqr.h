@@ -48,6 +48,7 @@ struct PcCall {
   void* Q; long long ldq;
   IoType io;
   bool cor;
+  bool notc;           // *_notc modes: both passes on the CUDA cores in plain fp32 (pc_gram_notc_kernel / pc_apply_notc_kernel)
   float* ws;           // base of the PC region
   PcLayout L;
 };

@@ -101,6 +101,7 @@ PcCall pc_call_of(const Plan& plan, int mode, const void* a, long long lda, void
   c.Q = q; c.ldq = ldq;
   c.io = mode_io(mode);
   c.cor = mode_is_cor(mode);
+  c.notc = !mode_is_tc(mode);
   c.ws = ws + plan.pc_off;
   c.L = plan.pcl;
   return c;

@@ -45,6 +45,7 @@ struct PassParams {
   void* Q;              // level output, column-major, same row count as A
   long long ldq;
   int emu;              // 0: fp32 products; 1 / 2 / 3: tf32_tc_nocor_emu / tf32_tc_cor_emu / mixed_tc_cor_emu operand rounding
+  const int* skip_ok;   // when set: the kernel returns at once if *skip_ok == kPcOk (the PC path did the work)
 };
 
 // rows-per-thread used for a given padded width
