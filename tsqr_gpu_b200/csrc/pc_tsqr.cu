@@ -737,14 +737,14 @@ __device__ __forceinline__ void solve_row(float (&y)[NP], const float* __restric
     for (int q = 0; q < p; ++q) {   // y_p -= z_q R[16q : 16q+16, 16p : 16p+16]; Rs[k][c] row-major, ld NP
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
-        const float z = y[16 * q + i];
+        const f32x2 nz = pack2(-y[16 * q + i], -y[16 * q + i]);
 #pragma unroll
-        for (int j4 = 0; j4 < 4; ++j4) {
+        for (int j4 = 0; j4 < 4; ++j4) {   // packed FMAs: two columns each
           const float4 r = *reinterpret_cast<const float4*>(Rs + (16 * q + i) * NP + 16 * p + 4 * j4);
-          y[16 * p + 4 * j4 + 0] = __fmaf_rn(-z, r.x, y[16 * p + 4 * j4 + 0]);
-          y[16 * p + 4 * j4 + 1] = __fmaf_rn(-z, r.y, y[16 * p + 4 * j4 + 1]);
-          y[16 * p + 4 * j4 + 2] = __fmaf_rn(-z, r.z, y[16 * p + 4 * j4 + 2]);
-          y[16 * p + 4 * j4 + 3] = __fmaf_rn(-z, r.w, y[16 * p + 4 * j4 + 3]);
+          const f32x2 d0 = fma2(nz, pack2(r.x, r.y), pack2(y[16 * p + 4 * j4 + 0], y[16 * p + 4 * j4 + 1]));
+          const f32x2 d1 = fma2(nz, pack2(r.z, r.w), pack2(y[16 * p + 4 * j4 + 2], y[16 * p + 4 * j4 + 3]));
+          unpack2(d0, y[16 * p + 4 * j4 + 0], y[16 * p + 4 * j4 + 1]);
+          unpack2(d1, y[16 * p + 4 * j4 + 2], y[16 * p + 4 * j4 + 3]);
         }
       }
     }
@@ -754,6 +754,23 @@ __device__ __forceinline__ void solve_row(float (&y)[NP], const float* __restric
     solve_panel16(yp, ci, p);
 #pragma unroll
     for (int j = 0; j < 16; ++j) y[16 * p + j] = yp[j];
+  }
+}
+
+// N consecutive floats (N = 1, 2, 4, 8) from an address aligned to min(N, 4) floats
+template <int N>
+__device__ __forceinline__ void ld_vec(const float* __restrict__ p, float (&v)[N]) {
+  if constexpr (N == 1) {
+    v[0] = p[0];
+  } else if constexpr (N == 2) {
+    const float2 x = *reinterpret_cast<const float2*>(p);
+    v[0] = x.x; v[1] = x.y;
+  } else {
+#pragma unroll
+    for (int i = 0; i < N / 4; ++i) {
+      const float4 x = *reinterpret_cast<const float4*>(p + 4 * i);
+      v[4 * i] = x.x; v[4 * i + 1] = x.y; v[4 * i + 2] = x.z; v[4 * i + 3] = x.w;
+    }
   }
 }
 
@@ -778,21 +795,24 @@ __global__ void __launch_bounds__(128, 3) pc_gram_notc_kernel(const PcParams P) 
   const TIo* A = reinterpret_cast<const TIo*>(P.A);
   for (int idx = t; idx < NP * NP; idx += 128) Rs[(idx % NP) * NP + idx / NP] = P.Rpre[idx];   // Rpre[k + c NP] -> Rs[k][c]
   __syncthreads();
-  float acc[RW][CW];
+  f32x2 acc[RW][CW / 2];   // fp32 pairs (columns 2j, 2j + 1)
 #pragma unroll
   for (int i = 0; i < RW; ++i)
 #pragma unroll
-    for (int j = 0; j < CW; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < CW / 2; ++j) acc[i][j] = 0ull;
   double* gp = P.Gpart + (size_t)blockIdx.x * NP * 128;   // slot of this CTA: entry (line i, column j) at j * 128 + i
   bool first_flush = true;
   auto flush = [&]() {
 #pragma unroll
     for (int i = 0; i < RW; ++i)
 #pragma unroll
-      for (int j = 0; j < CW; ++j) {
-        double* g = gp + (size_t)(CW * tx + j) * 128 + (RW * ty + i);
-        *g = (first_flush ? 0.0 : *g) + (double)acc[i][j];
-        acc[i][j] = 0.f;
+      for (int j = 0; j < CW / 2; ++j) {
+        float a0, a1;
+        unpack2(acc[i][j], a0, a1);
+        double* g = gp + (size_t)(CW * tx + 2 * j) * 128 + (RW * ty + i);
+        g[0] = (first_flush ? 0.0 : g[0]) + (double)a0;
+        g[128] = (first_flush ? 0.0 : g[128]) + (double)a1;
+        acc[i][j] = 0ull;
       }
     first_flush = false;
   };
@@ -812,14 +832,14 @@ __global__ void __launch_bounds__(128, 3) pc_gram_notc_kernel(const PcParams P) 
 #pragma unroll 4
     for (int k = 0; k < 128; ++k) {
       float a[RW], b[CW];
+      ld_vec<RW>(Zs + k * Sm::kZld + RW * ty, a);   // 128-/64-bit shared loads: the update is bound by them otherwise
+      ld_vec<CW>(Zs + k * Sm::kZld + CW * tx, b);
 #pragma unroll
-      for (int i = 0; i < RW; ++i) a[i] = Zs[k * Sm::kZld + RW * ty + i];
+      for (int i = 0; i < RW; ++i) {
+        const f32x2 aa = pack2(a[i], a[i]);
 #pragma unroll
-      for (int j = 0; j < CW; ++j) b[j] = Zs[k * Sm::kZld + CW * tx + j];
-#pragma unroll
-      for (int i = 0; i < RW; ++i)
-#pragma unroll
-        for (int j = 0; j < CW; ++j) acc[i][j] = __fmaf_rn(a[i], b[j], acc[i][j]);
+        for (int j = 0; j < CW / 2; ++j) acc[i][j] = fma2(aa, pack2(b[2 * j], b[2 * j + 1]), acc[i][j]);
+      }
     }
     if (++since == 16) { flush(); since = 0; }
   }
@@ -849,26 +869,28 @@ __global__ void __launch_bounds__(128, 3) pc_apply_notc_kernel(const PcParams P)
 #pragma unroll
     for (int c = 0; c < NP; ++c) y[c] = (valid && c < P.n) ? io_plain(A + row + (long long)c * P.lda) : 0.f;
     solve_row<NP>(y, ci, Rs);
-    float q[NP];
+    f32x2 q2[NP / 2];   // q[2c], q[2c + 1]
 #pragma unroll
-    for (int c = 0; c < NP; ++c) q[c] = 0.f;
+    for (int c = 0; c < NP / 2; ++c) q2[c] = 0ull;
 #pragma unroll 4
-    for (int k = 0; k < NP; ++k) {   // C is upper triangular, but a fixed trip count keeps the accumulators in registers
-      const float z = y[k];
+    for (int k = 0; k < NP; ++k) {   // (C = R_z^-1 B is a full matrix when a root factor B is applied); packed FMAs: two columns each
+      const f32x2 zz = pack2(y[k], y[k]);
 #pragma unroll
       for (int c4 = 0; c4 < NP / 4; ++c4) {
         const float4 cc = *reinterpret_cast<const float4*>(Cs + k * NP + 4 * c4);
-        q[4 * c4 + 0] = __fmaf_rn(z, cc.x, q[4 * c4 + 0]);
-        q[4 * c4 + 1] = __fmaf_rn(z, cc.y, q[4 * c4 + 1]);
-        q[4 * c4 + 2] = __fmaf_rn(z, cc.z, q[4 * c4 + 2]);
-        q[4 * c4 + 3] = __fmaf_rn(z, cc.w, q[4 * c4 + 3]);
+        q2[2 * c4] = fma2(zz, pack2(cc.x, cc.y), q2[2 * c4]);
+        q2[2 * c4 + 1] = fma2(zz, pack2(cc.z, cc.w), q2[2 * c4 + 1]);
       }
     }
     if (valid) {
       TIo* qp = Q + row;
 #pragma unroll
-      for (int c = 0; c < NP; ++c)
-        if (c < P.n) io_store(qp + (long long)c * P.ldq, q[c]);
+      for (int c2 = 0; c2 < NP / 2; ++c2) {
+        float q0, q1;
+        unpack2(q2[c2], q0, q1);
+        if (2 * c2 < P.n) io_store(qp + (long long)(2 * c2) * P.ldq, q0);
+        if (2 * c2 + 1 < P.n) io_store(qp + (long long)(2 * c2 + 1) * P.ldq, q1);
+      }
     }
   }
 }
