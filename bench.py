@@ -396,11 +396,12 @@ def main():
         # store/load of the tensor-core path is implementation traffic, not algorithmic bytes.
         balg_reduce, balg_build = 1.0 * m * n * esz, 2.0 * m * n * esz
         tc = lib.tsqr_b200_mode_uses_tensor_cores(tq.MODES[args.mode], m) != 0 and n <= 64
+        notc = args.mode.endswith("_notc")   # the fast path with CUDA-core passes
         # label -> (kernel, algorithmic bytes per launch): first pass reads A once, second pass reads it again
         # and writes Q; anything else a kernel moves is implementation traffic
         kernels = {
-            101: ("pc_gram_kernel (pass 1: Z = A R_pre^-1, Gram accumulation: read A once)", balg_reduce, "pc1"),
-            103: ("pc_apply_kernel (pass 2: Z again, Q = Z C: read A, write Q)", balg_build, "pc2"),
+            101: (("pc_gram_notc_kernel" if notc else "pc_gram_kernel") + " (pass 1: Z = A R_pre^-1, Gram accumulation: read A once)", balg_reduce, "pc1"),
+            103: (("pc_apply_notc_kernel" if notc else "pc_apply_kernel") + " (pass 2: Z again, Q = Z C: read A, write Q)", balg_build, "pc2"),
             0: (("cs_reduce_kernel" if tc else "ts_pass_kernel<REDUCE>") + " level 0 (R-reduce pass: read A once)", balg_reduce, "reduce"),
             1: (("tc_build_kernel" if tc else "ts_pass_kernel<BUILD>") + " level 0 (Q-build pass: read the slab, write Q)", balg_build, "build"),
         }
