@@ -809,7 +809,8 @@ __global__ void __launch_bounds__(128, 3) pc_gram_notc_kernel(const PcParams P) 
       for (int j = 0; j < CW / 2; ++j) {
         float a0, a1;
         unpack2(acc[i][j], a0, a1);
-        double* g = gp + (size_t)(CW * tx + 2 * j) * 128 + (RW * ty + i);
+        const int col = CW == 8 ? (2 * j < 4 ? 4 * tx + 2 * j : 32 + 4 * tx + 2 * j - 4) : CW * tx + 2 * j;   // see the b loads
+        double* g = gp + (size_t)col * 128 + (RW * ty + i);
         g[0] = (first_flush ? 0.0 : g[0]) + (double)a0;
         g[128] = (first_flush ? 0.0 : g[128]) + (double)a1;
         acc[i][j] = 0ull;
@@ -833,7 +834,15 @@ __global__ void __launch_bounds__(128, 3) pc_gram_notc_kernel(const PcParams P) 
     for (int k = 0; k < 128; ++k) {
       float a[RW], b[CW];
       ld_vec<RW>(Zs + k * Sm::kZld + RW * ty, a);   // 128-/64-bit shared loads: the update is bound by them otherwise
-      ld_vec<CW>(Zs + k * Sm::kZld + CW * tx, b);
+      if constexpr (CW == 8) {   // two groups of 4 columns, 32 apart: the 8 lanes of a quarter-warp read 128 contiguous bytes
+        float b0[4], b1[4];
+        ld_vec<4>(Zs + k * Sm::kZld + 4 * tx, b0);
+        ld_vec<4>(Zs + k * Sm::kZld + 32 + 4 * tx, b1);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { b[j] = b0[j]; b[4 + j] = b1[j]; }
+      } else {
+        ld_vec<CW>(Zs + k * Sm::kZld + CW * tx, b);
+      }
 #pragma unroll
       for (int i = 0; i < RW; ++i) {
         const f32x2 aa = pack2(a[i], a[i]);
