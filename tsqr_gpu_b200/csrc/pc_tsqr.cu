@@ -904,6 +904,96 @@ __global__ void __launch_bounds__(128, 3) pc_apply_notc_kernel(const PcParams P)
   }
 }
 
+// Pass 2 of fp32_notc at NP = 64 with the Q product register-blocked like the Gram update: the tile's Z goes through
+// shared memory (k-major), thread (ty, tx) computes rows [8 ty, +8) x columns {4 tx .. +3, 32 + 4 tx .. +3} of Q = Z C:
+// 4 LDS.128 per 64 FMAs instead of 16 broadcast LDS.128 -- the thread-per-row form is bound by exactly those loads.
+// Needs 16-byte aligned Q columns (the launcher checks); rows beyond M and columns beyond n are not stored.
+struct Notc2Smem {
+  static constexpr int kZld = 132;                       // k-major Z tile [64][kZld]
+  static constexpr uint32_t oR = 0;                      // R_pre row-major [64][64]
+  static constexpr uint32_t oC = oR + 64 * 64 * 4;       // C row-major [64][64]
+  static constexpr uint32_t oZ = oC + 64 * 64 * 4;
+  static constexpr uint32_t kBytes = oZ + 64 * kZld * 4;
+};
+template <int SLOT>
+__global__ void __launch_bounds__(128, 3) pc_apply_notc2_kernel(const PcParams P) {
+  constexpr int NP = 64;
+  using Sm = Notc2Smem;
+  extern __shared__ __align__(16) char sm[];
+  if (*P.status != kPcOk) return;
+  float* Rs = reinterpret_cast<float*>(sm + Sm::oR);
+  float* Cs = reinterpret_cast<float*>(sm + Sm::oC);
+  float* Zt = reinterpret_cast<float*>(sm + Sm::oZ);
+  const float* ci = cimg<SLOT>();
+  const int t = threadIdx.x, ty = t >> 3, tx = t & 7;
+  const float* A = reinterpret_cast<const float*>(P.A);
+  float* Q = reinterpret_cast<float*>(P.Q);
+  for (int idx = t; idx < NP * NP; idx += 128) {
+    Rs[(idx % NP) * NP + idx / NP] = P.Rpre[idx];
+    Cs[(idx % NP) * NP + idx / NP] = P.C[idx];
+  }
+  __syncthreads();
+  for (int tile = blockIdx.x; tile < P.tiles; tile += gridDim.x) {
+    const long long row = (long long)tile * kPcTileRows + t;
+    {
+      const bool valid = row < P.M;
+      float y[NP];
+#pragma unroll
+      for (int c = 0; c < NP; ++c) y[c] = (valid && c < P.n) ? A[row + (long long)c * P.lda] : 0.f;
+      solve_row<NP>(y, ci, Rs);
+      __syncthreads();   // the previous tile's product has read Zt
+#pragma unroll
+      for (int k = 0; k < NP; ++k) Zt[k * Sm::kZld + t] = y[k];
+    }
+    __syncthreads();
+    f32x2 acc[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0ull;
+#pragma unroll 2
+    for (int k = 0; k < NP; ++k) {
+      float a[8], b0[4], b1[4];
+      ld_vec<8>(Zt + k * Sm::kZld + 8 * ty, a);
+      ld_vec<4>(Cs + k * NP + 4 * tx, b0);
+      ld_vec<4>(Cs + k * NP + 32 + 4 * tx, b1);
+      const f32x2 bb[4] = {pack2(b0[0], b0[1]), pack2(b0[2], b0[3]), pack2(b1[0], b1[1]), pack2(b1[2], b1[3])};
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const f32x2 aa = pack2(a[i], a[i]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fma2(aa, bb[j], acc[i][j]);
+      }
+    }
+    // column of pair j, element e: j < 2: 4 tx + 2 j + e; else 32 + 4 tx + 2 (j - 2) + e; rows r0 .. r0 + 7
+    const long long r0 = (long long)tile * kPcTileRows + 8 * ty;
+    const bool full = r0 + 8 <= P.M;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int col = (j < 2 ? 4 * tx + 2 * j : 32 + 4 * tx + 2 * (j - 2)) + e;
+        if (col >= P.n) continue;
+        float v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float lo, hi;
+          unpack2(acc[i][j], lo, hi);
+          v[i] = e == 0 ? lo : hi;
+        }
+        float* qp = Q + r0 + (long long)col * P.ldq;
+        if (full) {
+          *reinterpret_cast<float4*>(qp) = make_float4(v[0], v[1], v[2], v[3]);
+          *reinterpret_cast<float4*>(qp + 4) = make_float4(v[4], v[5], v[6], v[7]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (r0 + i < P.M) qp[i] = v[i];
+        }
+      }
+  }
+}
+
 // ======================================================================================= finish
 // Stage 1, every CTA: fp64 sum of the per-CTA partials for 32 consecutive accumulator lanes of one Gram column
 // (warp w adds partials w, w + 8, ...: coalesced 256-byte reads, then the 8 warp sums are added in fixed order).
@@ -1287,10 +1377,30 @@ void launch_notc_slot(int slot, const PcParams& p, int grid, cudaStream_t s) {
     default: launch_notc_t<PASS, NP, TIo, 2>(p, grid, s); break;
   }
 }
+template <int SLOT>
+void launch_notc2_t(const PcParams& p, int grid, cudaStream_t s) {
+  auto kern = pc_apply_notc2_kernel<SLOT>;
+  static std::atomic<unsigned long long> smem_set{0};
+  set_smem_once(kern, (int)Notc2Smem::kBytes, smem_set);
+  kern<<<grid, 128, Notc2Smem::kBytes, s>>>(p);
+  note_launch();
+  TSQR_CUDA_CHECK(cudaGetLastError());
+}
 template <int PASS>
 void launch_notc(const PcCall& c, const PcParams& p, cudaStream_t s) {
   const int grid = (int)c.L.parts;
   const int slot = img_acquire(c.ws + c.L.cimg, s);
+  // pass 2, fp32, 64 padded columns, Q columns 16-byte aligned: the register-blocked form of the Q product
+  static const bool blocked = [] { const char* e = std::getenv("TSQR_B200_NOTC_BLOCKED"); return !(e && e[0] == '0'); }();
+  if (PASS == 2 && blocked && c.io == IoType::f32 && c.L.np == 64 && (reinterpret_cast<uintptr_t>(c.Q) & 15u) == 0 && (c.ldq % 4) == 0) {
+    switch (slot) {
+      case 0: launch_notc2_t<0>(p, grid, s); break;
+      case 1: launch_notc2_t<1>(p, grid, s); break;
+      default: launch_notc2_t<2>(p, grid, s); break;
+    }
+    img_release(slot, s);
+    return;
+  }
   if (c.io == IoType::f16) {
     switch (c.L.np) {
       case 16: launch_notc_slot<PASS, 16, __half>(slot, p, grid, s); break;
